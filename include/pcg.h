@@ -1,0 +1,166 @@
+/* pcg.h -- C ABI of libpcg.so: the B200 (sm_100a) point-cloud-codec graft.
+ *
+ * One shared object of hand-written CUDA kernels that replaces, for the learned codec's hot
+ * path, the native extensions the reference reaches through two un-vendored Python packages:
+ *   - MinkowskiEngine's pybind `_C` module (coordinate maps, kernel maps, sparse convolution,
+ *     pruning, interpolation)            -- reference call sites: model/transforms.py:32-166,
+ *     model/entropy_models.py:28-191,294,381,446, model/blocks.py:53, model/model.py:66-70,
+ *     147-161,227, utils.py:159, loss.py:105,185-188,221-271
+ *   - compressai's entropy-model arithmetic (EntropyBottleneck / GaussianConditional
+ *     likelihood, quantise, CDF index)   -- model/entropy_models.py:272-327,371-400,438-484
+ * Each entry point cites the reference interface it replaces.  See INTEGRATION.md for the
+ * ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name starts with h_; the caller allocates
+ *     every buffer (no ownership transfer); data-dependent sizes use a device counter
+ *     (`d_n_out`) the caller reads back, with the output buffer sized for the stated bound;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value 0 = ok, non-zero = error; pcg_last_error() gives a thread-local message;
+ *   - coordinates are rows of 4 x int32 (batch, x, y, z), 16-byte aligned, with
+ *     batch in [0, 32767] and x,y,z in [-32768, 32767] (they are packed into one 64-bit key);
+ *   - features are row-major fp32 (N x C) unless a bf16 shadow is named;
+ *   - kernel offsets follow MinkowskiEngine: odd k -> {-(k/2)..k/2}, even k -> {0..k-1},
+ *     offset index i = ix + k*iy + k*k*iz;
+ *   - a neighbour table `nbr` is int32 [K][n_out]: the input row feeding output row o through
+ *     kernel offset i, or -1.
+ */
+#ifndef PCG_H
+#define PCG_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCG_ACT_NONE 0
+#define PCG_ACT_RELU 1
+#define PCG_ACT_LEAKY_RELU 2 /* slope 0.01 (ME.MinkowskiLeakyReLU default) */
+
+const char *pcg_last_error(void);
+int pcg_version(void);
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+long pcg_launch_count(void);
+
+/* ---- scratch sizing (host helpers, no GPU work) ------------------------------------------ */
+long pcg_hash_capacity(long n_keys);            /* power of two >= 2*n_keys (min 1024) */
+size_t pcg_scratch_bytes(long n_items);         /* scratch needed by any compaction/select over n_items */
+
+/* ---- coordinate hash: replaces ME CoordinateMapGPU::insert_and_map (ME1) -------------------
+ * keys: uint64[cap], vals: int32[cap].  After build, lookup(c) = smallest row with coordinate c. */
+int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, void *stream);
+int pcg_hash_lookup(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *query, long nq,
+                    int32_t *rows_out, void *stream);
+
+/* First-occurrence unique rows (ME SparseTensor ctor dedupe; ME.utils.sparse_quantize, ME9).
+ * out_coords: up to n rows; out_index: source row of every kept row; table ends up mapping
+ * unique coordinate -> new row. */
+int pcg_unique_first(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap,
+                     int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
+                     size_t scratch_bytes, void *stream);
+
+/* Strided output coordinates floor(c/step)*step, first-occurrence order, + their hash table
+ * (ME CoordinateMapGPU::stride; used by every stride-2 MinkowskiConvolution and by
+ * transforms.py:166 down_conv whose output coordinates alone are consumed, a6). */
+int pcg_stride_coords(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
+                      int32_t *out_coords, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
+                      void *stream);
+
+/* Generative up-sampling coordinates unique{p + off_i*ts_out} over all rows and all ksize^3
+ * offsets, first-occurrence order (row major, offset minor) + their hash table
+ * (ME CoordinateMapGPU::stride_region; MinkowskiGenerativeConvolutionTranspose, ME3).
+ * out_coords must hold max_out rows; *d_n_out > max_out or a full table sets d_status[0]=1. */
+int pcg_generate_coords(const int32_t *coords, long n, int ksize, int ts_out, uint64_t *keys, int32_t *vals,
+                        long cap, int32_t *out_coords, long max_out, int32_t *d_n_out, int32_t *d_status,
+                        void *scratch, size_t scratch_bytes, void *stream);
+
+/* Kernel map (ME CoordinateMapGPU::kernel_map): nbr[i][o] = row of (out_coords[o] +/- off_i*ts)
+ * in the table of the INPUT coordinates.  transposed=0: in = out + off*ts (ts = input stride);
+ * transposed=1: in = out - off*ts (ts = output stride).  tile_mask (optional, may be NULL):
+ * uint32 [ceil(n_out/128)][4], bit i set when any row of the 128-row tile has a neighbour at
+ * offset i (ksize^3 <= 128 only). */
+int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
+                   int ksize, int ts, int transposed, int32_t *nbr, uint32_t *tile_mask, void *stream);
+
+/* Lexicographic (b,x,y,z) sort permutation: utils.py:142-187 sort_tensor / sort_points (a11). */
+int pcg_lexsort(const int32_t *coords, long n, int32_t *perm, void *scratch, size_t scratch_bytes, void *stream);
+size_t pcg_lexsort_scratch_bytes(long n);
+
+/* ---- sparse convolution: replaces ME ConvolutionForwardGPU / ConvolutionTransposeForwardGPU
+ * (ME2-ME4).  out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); accumulation order is fixed
+ * (offset index ascending, then input channel), so results are bit-reproducible run to run. */
+int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, int K, long n_out,
+                     const float *weight, const float *bias, int cout, int act, float *out, void *stream);
+
+/* bf16 tensor-core path (tcgen05, fp32 accumulation in TMEM).  cin % 64 == 0,
+ * cout % 16 == 0, 16 <= cout <= 256, K <= 128.  feats_bf16: N_in x cin bf16 rows;
+ * wpacked from pcg_pack_weights_bf16; out_f32 and/or out_bf16 may be NULL. */
+size_t pcg_packed_weight_bytes(int K, int cin, int cout);
+int pcg_pack_weights_bf16(const float *weight, int K, int cin, int cout, void *wpacked, void *stream);
+int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, const uint32_t *tile_mask,
+                    int K, long n_out, const void *wpacked, const float *bias, int cout, int act,
+                    float *out_f32, void *out_bf16, void *stream);
+int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
+
+/* Channel-wise convolution out[o][c] = sum_i F[nbr[i][o]][c] * w[i][c or 0]
+ * (ME.MinkowskiChannelwiseConvolution, loss.py:185-188; w_cols = C or 1). */
+int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, int K, long n_out, const float *w,
+                         int w_cols, float *out, void *stream);
+
+/* Elementwise activation on features (ME.MinkowskiReLU / MinkowskiLeakyReLU, ME7). */
+int pcg_activation(const float *x, long n, int act, float *out, void *stream);
+
+/* GDN1 / inverse GDN1 (model/blocks.py:26-57): norm = beta + |x| @ gamma^T; out = x/norm or x*norm.
+ * beta (C), gamma (C x C) are the re-parametrised values. */
+int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
+                void *stream);
+
+/* ---- occupancy top-k + prune (transforms.py:228-282, ME.MinkowskiPruning ME5) ---------------
+ * mask[i] = 1 for the k rows of batch `batch` with the largest logits (ties: smaller row first);
+ * rows of other batches are left untouched. */
+int pcg_topk_mask(const float *logits, const int32_t *coords, long n, int batch, long k, uint8_t *mask,
+                  void *scratch, size_t scratch_bytes, void *stream);
+/* Order-preserving row compaction of coords (may be NULL) and features (may be NULL) under mask. */
+int pcg_prune_rows(const int32_t *coords, const float *feats, long n, int c, const uint8_t *mask,
+                   int32_t *out_coords, float *out_feats, int32_t *d_n_out, void *scratch,
+                   size_t scratch_bytes, void *stream);
+
+/* ---- interpolation: SparseTensor.features_at_coordinates (ME6) ---------------------------------
+ * Trilinear over the 2^3 corners at spacing ts; absent corners contribute 0.  query: nq x 4 fp32. */
+int pcg_features_at(const uint64_t *keys, const int32_t *vals, long cap, const float *feats, int c, int ts,
+                    const float *query, long nq, float *out, void *stream);
+
+/* ---- entropy models (compressai 1.2.4, CAI1/CAI2) ------------------------------------------------
+ * Element (n, ch) of every operand lives at base[n*sn + ch*sc] (strides in elements), so both the
+ * (N,C) feature layout and the reference's (1,C,N) layout are addressable without a copy.
+ * EntropyBottleneck: eb_params is 58 floats per channel for filters (3,3,3,3):
+ *   per layer l: softplus(matrix_l) row-major, bias_l, tanh(factor_l) (no factor for the last). */
+int pcg_eb_likelihood(const float *x, long n, int c, long sn, long sc, const float *eb_params,
+                      float bound, float *lik, void *stream);
+/* mode 0: out_f = round(x - med) + med ("dequantize"); mode 1: out_i = (int) round(x - med). */
+int pcg_quantize(const float *x, const float *means, long n, int c, long sn, long sc, long msn, long msc,
+                 int mode, float *out_f, int32_t *out_i, void *stream);
+/* out = (float) sym + means  (EntropyModel.dequantize). */
+int pcg_dequantize(const int32_t *sym, const float *means, long n, int c, long sn, long sc, long msn, long msc,
+                   float *out, void *stream);
+/* GaussianConditional._likelihood: v=|x-mean|, s=max(scale,bound_scale);
+ * lik = max(Phi((.5-v)/s) - Phi((-.5-v)/s), bound). means may be NULL. */
+int pcg_gc_likelihood(const float *x, const float *scales, const float *means, long n, int c, long sn, long sc,
+                      float scale_bound, float lik_bound, float *lik, void *stream);
+/* GaussianConditional.build_indexes: idx = (T-1) - #{t in table[:-1] : max(s,bound) <= t}. */
+int pcg_gc_build_indexes(const float *scales, long n, int c, long sn, long sc, const float *table, int T,
+                         float scale_bound, int32_t *idx, void *stream);
+/* Fused reconstruction with learned offsets (entropy_models.py:218-233,469-481; a8):
+ *   sd = max(scales_hat*gain, bound); off = -quant_nn([gain, sd]); off = 0 where |q| < 1e-4;
+ *   y_hat = sign(q) * (|q| + off) * rescale + mean.
+ * q, scales_hat, means_hat, y_hat share (sn, sc); gain/rescale are per (row, channel) with strides
+ * (gsn, gsc).  mlp: 2->10->10->1 weights packed [W1(10x2) b1(10) W2(10x10) b2(10) W3(1x10) b3(1)]. */
+int pcg_gc_dequant_offsets(const float *q, const float *scales_hat, const float *means_hat, const float *gain,
+                           const float *rescale, long n, int c, long sn, long sc, long gsn, long gsc,
+                           const float *mlp, float scale_bound, float *y_hat, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCG_H */

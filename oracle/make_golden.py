@@ -1,0 +1,78 @@
+"""Generate tests/golden/*.npz by running the reference's UNMODIFIED model/*.py (from /root/reference) on top
+of the CPU oracle (oracle/shim.py).  TEST INFRASTRUCTURE; run in the build container only:
+
+    python -m oracle.make_golden
+
+The fixtures pin (a) oracle/pipeline_ref.py and (b) the product's host mirror + CUDA path against the
+reference's own orchestration code.  Widths are reduced (8 channels) so the state dict fits a small fixture;
+weights are random-init (torch.manual_seed) with the last analysis conv and the hyper-synthesis output scaled
+up so that the quantised symbols are not all zero (the reference ships no trained weights, README.md:122).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import yaml
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import shim, synth  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def small_config(name="CVPR_inverse_scaling", width=8):
+    cfg = yaml.safe_load(open(os.path.join(shim.REFERENCE, "configs", name + ".yaml")))["model"]
+    for sec in ("g_a", "g_s"):
+        for k in ("N1", "N2", "N3", "N4"):
+            cfg[sec][k] = width
+    cfg["entropy_model"]["C_bottleneck"] = width
+    cfg["entropy_model"]["C_hyper_bottleneck"] = width
+    return cfg
+
+
+def spread_weights(net):
+    with torch.no_grad():
+        net.g_a.down_conv_3[2].kernel.mul_(60.0)
+        net.entropy_model.h_a[4].kernel.mul_(30.0)
+        net.entropy_model.h_s[4].kernel.mul_(8.0)
+        net.entropy_model.h_s[4].bias.add_(0.5)
+    net.update()
+
+
+def make(name, cfg_name, seed, q):
+    cfg = small_config(cfg_name)
+    net = shim.reference_model(cfg, seed=seed)
+    spread_weights(net)
+    pts, rgb = synth.small_cloud(seed=seed + 1, radius=11.0, centre=(20, 20, 20), n_samples=9000)
+    pc = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1))
+    qt = torch.tensor([q], dtype=torch.float32)
+    with torch.no_grad():
+        bits, shapes, ks, coords, qv = net.compress(pc.clone(), qt, block_size=1024)
+        rec = net.decompress(coordinates=coords, strings=bits, shape=shapes, k=ks, q_vals=qv)
+        # eval-mode training forward (entropy_models.py:236-340) for likelihood parity
+        import MinkowskiEngine as ME
+        C4 = torch.cat([torch.zeros(len(pts), 1), torch.from_numpy(pts).float()], dim=1)
+        x = ME.SparseTensor(coordinates=C4, features=torch.from_numpy(rgb))
+        out = net(x, qt, torch.tensor([[1.0, 1.0]]))
+    sd = {k: v.numpy() for k, v in net.state_dict().items()}
+    np.savez_compressed(
+        os.path.join(OUT, name + ".npz"),
+        cfg_name=cfg_name, width=8, q=np.asarray(q, np.float32), points=pts, colors=rgb,
+        y_coords=coords[0].numpy(), k=np.asarray(ks[0]).reshape(-1), z_shape=np.asarray(shapes[0]),
+        y_string=np.frombuffer(bits[0][0][0], np.uint8), z_string=np.frombuffer(bits[0][1][0], np.uint8),
+        reconstruction=rec.numpy(),
+        fwd_pred_C=out["prediction"].C.numpy(), fwd_pred_F=out["prediction"].F.numpy(),
+        fwd_lik_y=out["likelihoods"]["y"].numpy(), fwd_lik_z=out["likelihoods"]["z"].numpy(),
+        fwd_occ3_C=out["occ_predictions"][2].C.numpy(), fwd_occ3_F=out["occ_predictions"][2].F.numpy(),
+        **{"sd/" + k: v for k, v in sd.items()})
+    print(name, "points", len(pts), "k", ks, "bytes y/z", len(bits[0][0][0]), len(bits[0][1][0]), "rec", tuple(rec.shape))
+
+
+if __name__ == "__main__":
+    assert shim.available(), "needs /root/reference"
+    os.makedirs(OUT, exist_ok=True)
+    make("ref_inverse_scaling", "CVPR_inverse_scaling", 0, (0.5, 0.5))
+    make("ref_inverse_nn", "CVPR_inverse_nn", 1, (0.2, 0.9))
+    make("ref_fixed_R1", "CVPR_inverse_scaling_fixed_R1", 2, (0.0, 0.0))

@@ -1,0 +1,123 @@
+"""Shared test helpers (also used by __graft_entry__.smoke())."""
+import os
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+BASE_CFG = {
+    "entropy_model": {"type": "MeanScaleHyperprior_map", "C_bottleneck": 128, "C_hyper_bottleneck": 192,
+                      "quantization_mode": "ste", "inverse_rescaling": True, "quantization_offset": True,
+                      "entropy_bottleneck_vbr": False},
+    "g_a": {"C_in": 4, "N1": 128, "N2": 128, "N3": 128, "N4": 128},
+    "g_s": {"C_out": 3, "N1": 128, "N2": 128, "N3": 128, "N4": 128},
+}
+
+
+def model_config(width=128, hyper=None, variant="inverse_scaling"):
+    """configs/CVPR_*.yaml `model:` section (widths optionally reduced for tests)."""
+    import copy
+    cfg = copy.deepcopy(BASE_CFG)
+    for sec in ("g_a", "g_s"):
+        for k in ("N1", "N2", "N3", "N4"):
+            cfg[sec][k] = width
+    cfg["entropy_model"]["C_bottleneck"] = width
+    cfg["entropy_model"]["C_hyper_bottleneck"] = hyper if hyper is not None else (192 if width == 128 else width)
+    if variant == "inverse_nn":
+        cfg["entropy_model"]["inverse_rescaling"] = False
+    elif variant == "fixed":
+        cfg["entropy_model"].update(inverse_rescaling=False, quantization_offset=False, adaptive_BN=False)
+    return cfg
+
+
+def spread_weights(net):
+    """Same perturbation as oracle/make_golden.py so quantised symbols are not all zero."""
+    with torch.no_grad():
+        net.g_a.down_conv_3[2].kernel.mul_(60.0)
+        net.entropy_model.h_a[4].kernel.mul_(30.0)
+        net.entropy_model.h_s[4].kernel.mul_(8.0)
+        net.entropy_model.h_s[4].bias.add_(0.5)
+    net.update()
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False)
+    sd = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/")}
+    return z, sd
+
+
+def golden_config(z):
+    variant = {"CVPR_inverse_scaling": "inverse_scaling", "CVPR_inverse_nn": "inverse_nn",
+               "CVPR_inverse_scaling_fixed_R1": "fixed"}[str(z["cfg_name"])]
+    return model_config(width=int(z["width"]), variant=variant)
+
+
+def coord_keys(C):
+    C = np.asarray(C).astype(np.int64)
+    if C.shape[1] == 3:
+        C = np.concatenate([np.zeros((len(C), 1), np.int64), C], axis=1)
+    return (C[:, 0] << 48) | ((C[:, 1] + 32768) << 32) | ((C[:, 2] + 32768) << 16) | (C[:, 3] + 32768)
+
+
+def align_rows(C_a, C_b):
+    """Indices (ia, ib) of the rows the two coordinate lists share, matched by coordinate."""
+    ka, kb = coord_keys(C_a), coord_keys(C_b)
+    common, ia, ib = np.intersect1d(ka, kb, return_indices=True)
+    return ia, ib
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def build_product_model(pkg, cfg, state_dict, device):
+    import importlib
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    net = model_mod.UnifiedModel(cfg)
+    missing, unexpected = net.load_state_dict({k: v for k, v in state_dict.items()}, strict=False)
+    bad = [k for k in missing if not k.split(".")[-1].startswith("_")]
+    assert not bad, f"state-dict keys missing in the product mirror: {bad}"
+    assert not [k for k in unexpected if not k.split(".")[-1].startswith("_")], f"unexpected keys: {unexpected}"
+    net = net.to(device).eval()
+    net.update()
+    return net
+
+
+def tiny_codec_roundtrip(pkg, device, width=32, seed=0):
+    """Encode + decode a small sphere on the GPU and check it against oracle/pipeline_ref.py on the same
+    weights: stride-8 coordinates and k bit-exact, symbols near-exact, decoded geometry/colours close."""
+    import importlib
+    from oracle import pipeline_ref, synth
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    cfg = model_config(width=width)
+    torch.manual_seed(seed)
+    net = model_mod.UnifiedModel(cfg)
+    spread_weights(net)
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    net = net.to(device).eval()
+    net.update()
+    pts, rgb = synth.small_cloud(seed=seed + 1, radius=11.0, centre=(20, 20, 20), n_samples=9000)
+    q = torch.tensor([[0.5, 0.5]], device=device)
+    x_block = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).to(device)
+    with torch.no_grad():
+        enc = net.encode_block(x_block, q)
+        y_sym = enc["y_symbols"]
+        x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: y_sym, enc["k"], q)
+        rec = net.finalize(x_hat.C, x_hat.F).cpu().numpy()
+    ref = pipeline_ref.RefCodec(sd, cfg)
+    renc = ref.encode_block(pts, rgb, [0.5, 0.5])
+    assert enc["k"] == renc["k"], (enc["k"], renc["k"])
+    assert (enc["y_points"].cpu().numpy() == renc["y_points"]).all(), "stride-8 coordinates differ"
+    assert (enc["z_points"].cpu().numpy() == renc["z_points"]).all(), "stride-32 coordinates differ"
+    ys, rys = enc["y_symbols"].cpu().numpy(), renc["y_symbols"]
+    frac = float((ys != rys).mean())
+    assert frac < 0.02 and np.abs(ys - rys).max() <= 1, f"y symbols differ on {frac:.3%} of elements"
+    rrec = ref.decode_block(renc["y_points"], renc["z_symbols"], renc["y_symbols"], renc["k"], [0.5, 0.5])
+    ia, ib = align_rows(rec[:, :3], rrec[:, :3])
+    assert len(rec) == len(rrec)
+    assert len(ia) >= 0.97 * len(rrec), f"decoded geometry overlap {len(ia)}/{len(rrec)}"
+    assert np.abs(rec[ia, 3:] - rrec[ib, 3:]).mean() < 0.02
+    return {"n": len(pts), "overlap": len(ia) / len(rrec), "symbol_mismatch": frac}

@@ -1,0 +1,46 @@
+"""The C-ABI library loads and exports every symbol include/pcg.h declares (no compute without a GPU)."""
+import ctypes
+import importlib
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "pcg.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(pcg_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__ as g
+    g.build()
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    lib = ctypes.CDLL(pkg._lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in pcg.h but not exported"
+    assert sorted(pkg._lib.exported_symbols()) == names, "ctypes prototypes and pcg.h disagree"
+
+
+def test_host_only_entry_points():
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    lib = pkg._lib.load()
+    assert lib.pcg_version() == 100
+    assert lib.pcg_hash_capacity(1000) == 2048 and lib.pcg_hash_capacity(3) == 1024
+    assert lib.pcg_scratch_bytes(10_000) > 10_000
+    assert lib.pcg_packed_weight_bytes(27, 128, 64) == 27 * 2 * 64 * 128
+    assert lib.pcg_launch_count() == 0
+
+
+def test_cpu_tensors_are_rejected_loudly():
+    import pytest
+    import torch
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    with pytest.raises(RuntimeError, match="no CPU path|CUDA"):
+        pkg.sparse_ops.CoordSet(torch.zeros((4, 4), dtype=torch.int32), 1)
+    me = importlib.import_module(pkg.__name__ + ".MinkowskiEngine")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        me.SparseTensor(torch.zeros(4, 1), torch.zeros((4, 4), dtype=torch.int32))

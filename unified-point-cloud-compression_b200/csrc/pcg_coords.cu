@@ -1,0 +1,430 @@
+// Coordinate hash, strided / generative coordinate sets, kernel maps, pruning, lexsort.
+// HBM-bound integer work: int4 coordinate loads, 64-bit packed keys, open addressing.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "pcg_compact.cuh"
+
+// ---------------------------------------------------------------------------- scan of block counts
+__global__ void __launch_bounds__(1024) k_scan_block_counts(int32_t *counts, long n, int32_t *d_total) {
+    __shared__ int warp_sums[32];
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long base = 0; base < n; base += 1024) {
+        long i = base + threadIdx.x;
+        int v = i < n ? counts[i] : 0;
+        int incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_sums[lane], wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int t = __shfl_up_sync(0xffffffffu, wi, d);
+                if (lane >= d) wi += t;
+            }
+            warp_sums[lane] = wi - w;
+        }
+        __syncthreads();
+        int carry = carry_s;
+        int excl = carry + warp_sums[warp] + incl - v;
+        if (i < n) counts[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) d_total[0] = carry_s;
+}
+
+int pcg_scan_block_counts(int32_t *block_counts, long n_blocks, int32_t *d_total, cudaStream_t st) {
+    k_scan_block_counts<<<1, 1024, 0, st>>>(block_counts, n_blocks, d_total);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- hash build / lookup
+__global__ void k_table_clear(uint64_t *keys, int32_t *vals, long cap) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long stride = (long)gridDim.x * blockDim.x;
+    for (; i < cap; i += stride) {
+        keys[i] = PCG_EMPTY_KEY;
+        vals[i] = 0x7fffffff;
+    }
+}
+
+__global__ void k_hash_insert(const int32_t *__restrict__ coords, long n, uint64_t *keys, int32_t *vals, uint64_t mask) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int4 c = pcg_ld_coord(coords, i);
+    pcg_table_insert_min(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w), (int)i);
+}
+
+__global__ void k_hash_lookup(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals, uint64_t mask,
+                              const int32_t *__restrict__ query, long nq, int32_t *rows) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    int4 c = pcg_ld_coord(query, i);
+    rows[i] = pcg_in_range(c.x, c.y, c.z, c.w) ? pcg_table_find(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w)) : -1;
+}
+
+static int clear_table(uint64_t *keys, int32_t *vals, long cap, cudaStream_t st) {
+    long blocks = cdiv(cap, 256 * 8);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    k_table_clear<<<(unsigned)blocks, 256, 0, st>>>(keys, vals, cap);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+static bool is_pow2(long v) { return v > 0 && (v & (v - 1)) == 0; }
+
+extern "C" long pcg_hash_capacity(long n_keys) {
+    long cap = 1024;
+    while (cap < 2 * n_keys) cap <<= 1;
+    return cap;
+}
+
+extern "C" size_t pcg_scratch_bytes(long n_items) { return pcg_compact_scratch_bytes(n_items) + 8192; }
+
+extern "C" int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, void *stream) {
+    PCG_CHECK_ARG(is_pow2(cap) && cap >= n + 1, "pcg_hash_build: cap=%ld must be a power of two > n=%ld", cap, n);
+    cudaStream_t st = as_stream(stream);
+    if (int rc = clear_table(keys, vals, cap, st)) return rc;
+    if (n > 0) {
+        k_hash_insert<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, keys, vals, (uint64_t)cap - 1);
+        PCG_LAUNCHED();
+    }
+    return 0;
+}
+
+extern "C" int pcg_hash_lookup(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *query, long nq,
+                               int32_t *rows_out, void *stream) {
+    PCG_CHECK_ARG(is_pow2(cap), "pcg_hash_lookup: cap=%ld must be a power of two", cap);
+    if (nq <= 0) return 0;
+    k_hash_lookup<<<(unsigned)cdiv(nq, 256), 256, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, query, nq, rows_out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- unique / stride
+struct StridedKey {  // key of floor(c/step)*step for row i
+    const int32_t *coords;
+    int step;
+    __device__ __forceinline__ int4 coord(long i) const {
+        int4 c = pcg_ld_coord(coords, i);
+        if (step > 1) { c.y = pcg_floor_to(c.y, step); c.z = pcg_floor_to(c.z, step); c.w = pcg_floor_to(c.w, step); }
+        return c;
+    }
+};
+
+__global__ void k_insert_strided(StridedKey sk, long n, uint64_t *keys, int32_t *vals, uint64_t mask) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int4 c = sk.coord(i);
+    pcg_table_insert_min(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w), (int)i);
+}
+
+struct FlagFirstStrided {
+    StridedKey sk;
+    const uint64_t *keys;
+    const int32_t *vals;
+    uint64_t mask;
+    __device__ bool operator()(long i) const {
+        int4 c = sk.coord(i);
+        return pcg_table_find(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w)) == (int)i;
+    }
+};
+
+struct EmitStrided {
+    StridedKey sk;
+    int32_t *out_coords;
+    int32_t *out_index;  // may be null
+    __device__ void operator()(long i, int rank) const {
+        int4 c = sk.coord(i);
+        reinterpret_cast<int4 *>(out_coords)[rank] = c;
+        if (out_index) out_index[rank] = (int)i;
+    }
+};
+
+// after compaction: table value (first source row) -> new row id
+__global__ void k_remap_table(const int32_t *__restrict__ out_coords, const int32_t *d_n_out, long max_out,
+                              const uint64_t *keys, int32_t *vals, uint64_t mask) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long n = d_n_out[0];
+    if (n > max_out) n = max_out;
+    long stride = (long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int4 c = pcg_ld_coord(out_coords, i);
+        uint64_t key = pcg_pack(c.x, c.y, c.z, c.w);
+        uint64_t s = pcg_mix(key) & mask;
+        for (uint64_t probes = 0; probes <= mask && keys[s] != key; ++probes) s = (s + 1) & mask;
+        if (keys[s] == key) vals[s] = (int)i;
+    }
+}
+
+static int unique_strided(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
+                          int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
+                          size_t scratch_bytes, cudaStream_t st) {
+    PCG_CHECK_ARG(is_pow2(cap) && cap >= n + 1, "unique/stride: cap=%ld must be a power of two > n=%ld", cap, n);
+    PCG_CHECK_ARG(step >= 1, "unique/stride: step=%d", step);
+    PcgScratch s;
+    PCG_CHECK_ARG(pcg_carve_scratch(scratch, scratch_bytes, n, s), "unique/stride: scratch too small (%zu < %zu)",
+                  scratch_bytes, pcg_compact_scratch_bytes(n));
+    if (int rc = clear_table(keys, vals, cap, st)) return rc;
+    if (n <= 0) {
+        PCG_CUDA(cudaMemsetAsync(d_n_out, 0, sizeof(int32_t), st));
+        return 0;
+    }
+    StridedKey sk{coords, step};
+    uint64_t mask = (uint64_t)cap - 1;
+    k_insert_strided<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(sk, n, keys, vals, mask);
+    PCG_LAUNCHED();
+    if (int rc = pcg_compact(n, FlagFirstStrided{sk, keys, vals, mask}, EmitStrided{sk, out_coords, out_index}, d_n_out, s, st))
+        return rc;
+    long blocks = cdiv(n, 256);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    k_remap_table<<<(unsigned)blocks, 256, 0, st>>>(out_coords, d_n_out, n, keys, vals, mask);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+extern "C" int pcg_unique_first(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap,
+                                int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
+                                size_t scratch_bytes, void *stream) {
+    return unique_strided(coords, n, 1, keys, vals, cap, out_coords, out_index, d_n_out, scratch, scratch_bytes,
+                          as_stream(stream));
+}
+
+extern "C" int pcg_stride_coords(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
+                                 int32_t *out_coords, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
+                                 void *stream) {
+    return unique_strided(coords, n, step, keys, vals, cap, out_coords, nullptr, d_n_out, scratch, scratch_bytes,
+                          as_stream(stream));
+}
+
+// ---------------------------------------------------------------------------- generative coords
+struct GenKey {
+    const int32_t *coords;
+    int ksize, K, ts_out;
+    __device__ __forceinline__ int4 coord(long cand) const {
+        long row = cand / K;
+        int k = (int)(cand - row * K);
+        int4 c = pcg_ld_coord(coords, row);
+        int dx, dy, dz;
+        pcg_kernel_offset(k, ksize, dx, dy, dz);
+        c.y += dx * ts_out; c.z += dy * ts_out; c.w += dz * ts_out;
+        return c;
+    }
+};
+
+__global__ void k_insert_generated(GenKey gk, long n_cand, uint64_t *keys, int32_t *vals, uint64_t mask, int32_t *d_status) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cand) return;
+    int4 c = gk.coord(i);
+    if (!pcg_in_range(c.x, c.y, c.z, c.w)) { atomicOr(d_status, 2); return; }
+    // candidate ids can exceed int32 only for n*K > 2^31, rejected on the host side
+    if (pcg_table_insert_min(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w), (int)i) < 0) atomicOr(d_status, 1);
+}
+
+struct FlagFirstGen {
+    GenKey gk;
+    const uint64_t *keys;
+    const int32_t *vals;
+    uint64_t mask;
+    __device__ bool operator()(long i) const {
+        int4 c = gk.coord(i);
+        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
+        return pcg_table_find(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w)) == (int)i;
+    }
+};
+
+struct EmitGen {
+    GenKey gk;
+    int32_t *out_coords;
+    long max_out;
+    __device__ void operator()(long i, int rank) const {
+        if (rank < max_out) reinterpret_cast<int4 *>(out_coords)[rank] = gk.coord(i);
+    }
+};
+
+__global__ void k_flag_overflow(const int32_t *d_n_out, long max_out, int32_t *d_status) {
+    if (d_n_out[0] > max_out) atomicOr(d_status, 1);
+}
+
+extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int ts_out, uint64_t *keys, int32_t *vals,
+                                   long cap, int32_t *out_coords, long max_out, int32_t *d_n_out, int32_t *d_status,
+                                   void *scratch, size_t scratch_bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    PCG_CHECK_ARG(ksize >= 1 && ksize <= 9 && ts_out >= 1, "pcg_generate_coords: ksize=%d ts_out=%d", ksize, ts_out);
+    int K = ksize * ksize * ksize;
+    long n_cand = n * (long)K;
+    PCG_CHECK_ARG(n_cand < 2147483647L, "pcg_generate_coords: %ld candidates exceed int32", n_cand);
+    PCG_CHECK_ARG(is_pow2(cap), "pcg_generate_coords: cap=%ld must be a power of two", cap);
+    PcgScratch s;
+    PCG_CHECK_ARG(pcg_carve_scratch(scratch, scratch_bytes, n_cand, s), "pcg_generate_coords: scratch too small (%zu < %zu)",
+                  scratch_bytes, pcg_compact_scratch_bytes(n_cand));
+    PCG_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    if (int rc = clear_table(keys, vals, cap, st)) return rc;
+    if (n <= 0) {
+        PCG_CUDA(cudaMemsetAsync(d_n_out, 0, sizeof(int32_t), st));
+        return 0;
+    }
+    GenKey gk{coords, ksize, K, ts_out};
+    uint64_t mask = (uint64_t)cap - 1;
+    k_insert_generated<<<(unsigned)cdiv(n_cand, 256), 256, 0, st>>>(gk, n_cand, keys, vals, mask, d_status);
+    PCG_LAUNCHED();
+    if (int rc = pcg_compact(n_cand, FlagFirstGen{gk, keys, vals, mask}, EmitGen{gk, out_coords, max_out}, d_n_out, s, st))
+        return rc;
+    k_flag_overflow<<<1, 1, 0, st>>>(d_n_out, max_out, d_status);
+    PCG_LAUNCHED();
+    long blocks = cdiv(max_out, 256);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    if (blocks < 1) blocks = 1;
+    k_remap_table<<<(unsigned)blocks, 256, 0, st>>>(out_coords, d_n_out, max_out, keys, vals, mask);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- kernel map
+// One CTA = one 128-row output tile; thread r owns row r and walks all K offsets, so the
+// coordinate is loaded once (int4) and nbr[k][tile rows] is written as one coalesced 512 B line.
+__global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
+                                                    uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
+                                                    int ksize, int K, int step, int32_t *__restrict__ nbr,
+                                                    uint32_t *__restrict__ tile_mask) {
+    long o = (long)blockIdx.x * 128 + threadIdx.x;
+    bool live = o < n_out;
+    int4 c = live ? pcg_ld_coord(out_coords, o) : make_int4(0, 0, 0, 0);
+    __shared__ uint32_t smask[4];
+    if (threadIdx.x < 4) smask[threadIdx.x] = 0;
+    __syncthreads();
+    const int lo = (ksize & 1) ? -(ksize >> 1) : 0;
+    int k = 0;
+    for (int iz = 0; iz < ksize; ++iz)
+        for (int iy = 0; iy < ksize; ++iy)
+            for (int ix = 0; ix < ksize; ++ix, ++k) {
+                int row = -1;
+                if (live) {
+                    int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
+                    if (pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
+                    nbr[(long)k * n_out + o] = row;
+                }
+                if (tile_mask) {
+                    unsigned any = __ballot_sync(0xffffffffu, row >= 0);
+                    if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
+                }
+            }
+    if (tile_mask) {
+        __syncthreads();
+        if (threadIdx.x < 4) tile_mask[(long)blockIdx.x * 4 + threadIdx.x] = smask[threadIdx.x];
+    }
+}
+
+extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
+                              int ksize, int ts, int transposed, int32_t *nbr, uint32_t *tile_mask, void *stream) {
+    PCG_CHECK_ARG(is_pow2(cap), "pcg_kernel_map: cap=%ld must be a power of two", cap);
+    PCG_CHECK_ARG(ksize >= 1 && ksize <= 9 && ts >= 1, "pcg_kernel_map: ksize=%d ts=%d", ksize, ts);
+    int K = ksize * ksize * ksize;
+    PCG_CHECK_ARG(tile_mask == nullptr || K <= 128, "pcg_kernel_map: tile_mask needs ksize^3 <= 128 (got %d)", K);
+    if (n_out <= 0) return 0;
+    int step = transposed ? -ts : ts;
+    k_kernel_map<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
+                                                                           ksize, K, step, nbr, tile_mask);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- prune rows
+struct FlagMask {
+    const uint8_t *mask;
+    __device__ bool operator()(long i) const { return mask[i] != 0; }
+};
+struct EmitCoordIndex {
+    const int32_t *coords;
+    int32_t *out_coords;
+    int32_t *rank_of;  // rank_of[rank] = source row
+    __device__ void operator()(long i, int rank) const {
+        if (coords) reinterpret_cast<int4 *>(out_coords)[rank] = pcg_ld_coord(coords, i);
+        rank_of[rank] = (int)i;
+    }
+};
+
+// copy kept feature rows: one warp per output row, float4 lanes when C % 4 == 0
+__global__ void k_gather_rows(const float *__restrict__ feats, int c, const int32_t *__restrict__ src_rows,
+                              const int32_t *d_n, float *__restrict__ out) {
+    long n = d_n[0];
+    long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    long nwarps = ((long)gridDim.x * blockDim.x) >> 5;
+    for (long r = warp; r < n; r += nwarps) {
+        const float *src = feats + (long)src_rows[r] * c;
+        float *dst = out + r * c;
+        if ((c & 3) == 0) {
+            for (int j = lane; j < (c >> 2); j += 32)
+                reinterpret_cast<float4 *>(dst)[j] = __ldg(reinterpret_cast<const float4 *>(src) + j);
+        } else {
+            for (int j = lane; j < c; j += 32) dst[j] = __ldg(src + j);
+        }
+    }
+}
+
+extern "C" int pcg_prune_rows(const int32_t *coords, const float *feats, long n, int c, const uint8_t *mask,
+                              int32_t *out_coords, float *out_feats, int32_t *d_n_out, void *scratch,
+                              size_t scratch_bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    // scratch: compaction scratch + n int32 source-row list
+    size_t need = pcg_compact_scratch_bytes(n) + (size_t)(n > 0 ? n : 1) * sizeof(int32_t);
+    PCG_CHECK_ARG(scratch && scratch_bytes >= need, "pcg_prune_rows: scratch too small (%zu < %zu)", scratch_bytes, need);
+    PcgScratch s;
+    pcg_carve_scratch(scratch, scratch_bytes, n, s);
+    int32_t *src_rows = reinterpret_cast<int32_t *>(reinterpret_cast<uint8_t *>(scratch) + pcg_compact_scratch_bytes(n));
+    if (int rc = pcg_compact(n, FlagMask{mask}, EmitCoordIndex{coords, out_coords, src_rows}, d_n_out, s, st)) return rc;
+    if (feats && n > 0) {
+        long blocks = cdiv(n * 32, 256);
+        if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+        k_gather_rows<<<(unsigned)blocks, 256, 0, st>>>(feats, c, src_rows, d_n_out, out_feats);
+        PCG_LAUNCHED();
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- lexsort
+__global__ void k_pack_keys(const int32_t *__restrict__ coords, long n, uint64_t *keys, int32_t *idx) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int4 c = pcg_ld_coord(coords, i);
+    keys[i] = pcg_pack(c.x, c.y, c.z, c.w);
+    idx[i] = (int)i;
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+extern "C" size_t pcg_lexsort_scratch_bytes(long n) {
+    size_t temp = 0;
+    long m = n > 0 ? n : 1;
+    cub::DeviceRadixSort::SortPairs(nullptr, temp, (const uint64_t *)nullptr, (uint64_t *)nullptr, (const int32_t *)nullptr,
+                                    (int32_t *)nullptr, (int)m);
+    return align256(temp) + 2 * align256((size_t)m * 8) + align256((size_t)m * 4) + 256;
+}
+
+extern "C" int pcg_lexsort(const int32_t *coords, long n, int32_t *perm, void *scratch, size_t scratch_bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    if (n <= 0) return 0;
+    PCG_CHECK_ARG(scratch && scratch_bytes >= pcg_lexsort_scratch_bytes(n), "pcg_lexsort: scratch too small");
+    uint8_t *p = reinterpret_cast<uint8_t *>(scratch);
+    uint64_t *k_in = reinterpret_cast<uint64_t *>(p); p += align256((size_t)n * 8);
+    uint64_t *k_out = reinterpret_cast<uint64_t *>(p); p += align256((size_t)n * 8);
+    int32_t *i_in = reinterpret_cast<int32_t *>(p); p += align256((size_t)n * 4);
+    size_t temp = scratch_bytes - (size_t)(p - reinterpret_cast<uint8_t *>(scratch));
+    k_pack_keys<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, k_in, i_in);
+    PCG_LAUNCHED();
+    // plumbing: CUB's radix sort orders the packed 64-bit keys (stable)
+    PCG_CUDA(cub::DeviceRadixSort::SortPairs(p, temp, k_in, k_out, i_in, perm, (int)n, 0, 64, st));
+    pcg_launches.fetch_add(1, std::memory_order_relaxed);
+    return 0;
+}

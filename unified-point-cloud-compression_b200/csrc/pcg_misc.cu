@@ -1,0 +1,266 @@
+// Activation, GDN1, occupancy top-k (radix select), trilinear feature lookup, bf16 cast.
+#include "pcg_compact.cuh"
+
+// ---------------------------------------------------------------------------- activation / cast
+__global__ void k_activation(const float *__restrict__ x, long n, int act, float *__restrict__ out) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long stride = (long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = pcg_apply_act(x[i], act);
+}
+
+extern "C" int pcg_activation(const float *x, long n, int act, float *out, void *stream) {
+    if (n <= 0) return 0;
+    long blocks = cdiv(n, 256);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    k_activation<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(x, n, act, out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+__global__ void k_f32_to_bf16(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, long n) {
+    long i = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    long stride = (long)gridDim.x * blockDim.x * 4;
+    for (; i < n; i += stride) {
+        if (i + 3 < n) {
+            float4 v = __ldg(reinterpret_cast<const float4 *>(src + i));
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t *>(&lo);
+            pk.y = *reinterpret_cast<uint32_t *>(&hi);
+            *reinterpret_cast<uint2 *>(dst + i) = pk;
+        } else {
+            for (long j = i; j < n; ++j) dst[j] = __float2bfloat16_rn(src[j]);
+        }
+    }
+}
+
+extern "C" int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream) {
+    if (n <= 0) return 0;
+    PCG_CHECK_ARG(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 7) == 0, "pcg_f32_to_bf16: unaligned buffers");
+    long blocks = cdiv(n, 256 * 4);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    k_f32_to_bf16<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(src, reinterpret_cast<__nv_bfloat16 *>(dst), n);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- GDN1
+// norm[n][j] = beta[j] + sum_i gamma[j][i] * |x[n][i]|;  out = x * (1/norm)  or  x * norm.
+// 64x64 output tile per CTA, 16-deep smem stages, fixed ascending-i accumulation.
+__global__ void __launch_bounds__(256) k_gdn(const float *__restrict__ x, long n, int c, const float *__restrict__ beta,
+                                             const float *__restrict__ gamma, int inverse, float *__restrict__ out) {
+    __shared__ __align__(16) float As[16][64 + 4];
+    __shared__ __align__(16) float Bs[16][64 + 4];
+    const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
+    const long row0 = (long)blockIdx.x * 64;
+    const int col0 = blockIdx.y * 64;
+    float acc[4][4] = {};
+    for (int k0 = 0; k0 < c; k0 += 16) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            int idx = t + 256 * e;
+            {   // A: |x[row0 + r][k0 + kk]|, idx -> (r = idx/16, kk = idx%16) coalesced along kk
+                int r = idx >> 4, kk = idx & 15;
+                long o = row0 + r;
+                As[kk][r] = (o < n && k0 + kk < c) ? fabsf(__ldg(x + o * c + k0 + kk)) : 0.f;
+            }
+            {   // B[kk][j] = gamma[col0 + j][k0 + kk]
+                int j = idx >> 4, kk = idx & 15;
+                Bs[kk][j] = (col0 + j < c && k0 + kk < c) ? __ldg(gamma + (long)(col0 + j) * c + k0 + kk) : 0.f;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            float4 a = *reinterpret_cast<const float4 *>(&As[kk][ty * 4]);
+            float4 b = *reinterpret_cast<const float4 *>(&Bs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        long o = row0 + ty * 4 + i;
+        if (o >= n) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int col = col0 + tx * 4 + j;
+            if (col < c) {
+                float nv = acc[i][j] + __ldg(beta + col);
+                float xv = __ldg(x + o * c + col);
+                out[o * c + col] = inverse ? xv * nv : xv * (1.0f / nv);
+            }
+        }
+    }
+}
+
+extern "C" int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
+                           void *stream) {
+    if (n <= 0) return 0;
+    dim3 grid((unsigned)cdiv(n, 64), (unsigned)cdiv(c, 64));
+    k_gdn<<<grid, 256, 0, as_stream(stream)>>>(x, n, c, beta, gamma, inverse, out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------- top-k mask (radix select)
+struct TopkState {
+    uint32_t prefix;       // selected high digits so far
+    uint32_t prefix_mask;  // which bits of prefix are decided
+    long long k_rem;       // how many still to take among keys matching prefix
+    int hist[256];
+};
+
+__device__ __forceinline__ uint32_t pcg_order_key(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // larger float -> larger key
+}
+
+__global__ void k_topk_init(TopkState *s, long k) {
+    if (threadIdx.x == 0) { s->prefix = 0; s->prefix_mask = 0; s->k_rem = k; }
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s->hist[i] = 0;
+}
+
+__global__ void k_topk_hist(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int batch,
+                            int shift, TopkState *s) {
+    __shared__ int h[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = s->prefix, pmask = s->prefix_mask;
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long stride = (long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        if (coords && __ldg(coords + 4 * i) != batch) continue;
+        uint32_t key = pcg_order_key(__ldg(logits + i));
+        if ((key & pmask) == prefix) atomicAdd(&h[(key >> shift) & 255], 1);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 256; j += blockDim.x)
+        if (h[j]) atomicAdd(&s->hist[j], h[j]);
+}
+
+__global__ void k_topk_select(TopkState *s, int shift) {
+    // single thread: walk digits from the top until the cumulative count reaches k_rem
+    if (threadIdx.x == 0) {
+        long long k = s->k_rem, total = 0;
+        for (int d = 0; d < 256; ++d) total += s->hist[d];
+        if (k > total) k = total;          // fewer rows than k: take them all
+        int d = 255;
+        long long above = 0;
+        if (k > 0) {
+            for (; d > 0; --d) {
+                if (above + s->hist[d] >= k) break;
+                above += s->hist[d];
+            }
+        } else {
+            d = 255; above = 0;
+        }
+        s->prefix |= ((uint32_t)d << shift);
+        s->prefix_mask |= (255u << shift);
+        s->k_rem = k - above;              // to take among keys with this digit (0 when k == 0)
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s->hist[i] = 0;
+}
+
+__global__ void k_topk_above(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int batch,
+                             const TopkState *s, uint8_t *mask) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (coords && __ldg(coords + 4 * i) != batch) return;
+    uint32_t key = pcg_order_key(__ldg(logits + i));
+    // strictly above the threshold key; with k_rem == 0 and the all-ones prefix nothing qualifies
+    mask[i] = (key > s->prefix) ? 1 : 0;
+}
+
+struct FlagTie {
+    const float *logits;
+    const int32_t *coords;
+    int batch;
+    const TopkState *s;
+    __device__ bool operator()(long i) const {
+        if (coords && __ldg(coords + 4 * i) != batch) return false;
+        return pcg_order_key(__ldg(logits + i)) == s->prefix;
+    }
+};
+struct EmitTie {
+    const TopkState *s;
+    uint8_t *mask;
+    __device__ void operator()(long i, int rank) const {
+        if ((long long)rank < s->k_rem) mask[i] = 1;
+    }
+};
+
+extern "C" int pcg_topk_mask(const float *logits, const int32_t *coords, long n, int batch, long k, uint8_t *mask,
+                             void *scratch, size_t scratch_bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    if (n <= 0) return 0;
+    PCG_CHECK_ARG(k >= 0, "pcg_topk_mask: k=%ld", k);
+    size_t need = pcg_compact_scratch_bytes(n) + 2048;
+    PCG_CHECK_ARG(scratch && scratch_bytes >= need, "pcg_topk_mask: scratch too small (%zu < %zu)", scratch_bytes, need);
+    PcgScratch cs;
+    pcg_carve_scratch(scratch, scratch_bytes, n, cs);
+    uintptr_t sp = (uintptr_t)scratch + pcg_compact_scratch_bytes(n);
+    sp = (sp + 255) & ~(uintptr_t)255;
+    TopkState *s = reinterpret_cast<TopkState *>(sp);
+    int32_t *d_dummy = reinterpret_cast<int32_t *>(sp + 1536);
+    k_topk_init<<<1, 256, 0, st>>>(s, k);
+    PCG_LAUNCHED();
+    long blocks = cdiv(n, 256 * 4);
+    if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        k_topk_hist<<<(unsigned)blocks, 256, 0, st>>>(logits, coords, n, batch, shift, s);
+        PCG_LAUNCHED();
+        k_topk_select<<<1, 256, 0, st>>>(s, shift);
+        PCG_LAUNCHED();
+    }
+    k_topk_above<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(logits, coords, n, batch, s, mask);
+    PCG_LAUNCHED();
+    return pcg_compact(n, FlagTie{logits, coords, batch, s}, EmitTie{s, mask}, d_dummy, cs, st);
+}
+
+// ---------------------------------------------------------------------------- features_at_coordinates
+// one warp per query; lanes 0..7 resolve the 8 corners, then all lanes stride the channels
+__global__ void k_features_at(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals, uint64_t mask,
+                              const float *__restrict__ feats, int c, int ts, const float *__restrict__ query, long nq,
+                              float *__restrict__ out) {
+    long q = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    float4 qv = __ldg(reinterpret_cast<const float4 *>(query) + q);
+    int row = -1;
+    float w = 0.f;
+    if (lane < 8) {
+        const float fts = (float)ts;
+        float bx = floorf(qv.y / fts) * fts, by = floorf(qv.z / fts) * fts, bz = floorf(qv.w / fts) * fts;
+        float fx = (qv.y - bx) / fts, fy = (qv.z - by) / fts, fz = (qv.w - bz) / fts;
+        int dx = lane & 1, dy = (lane >> 1) & 1, dz = (lane >> 2) & 1;
+        w = (dx ? fx : 1.f - fx) * (dy ? fy : 1.f - fy) * (dz ? fz : 1.f - fz);
+        int b = (int)qv.x, x = (int)bx + dx * ts, y = (int)by + dy * ts, z = (int)bz + dz * ts;
+        if (w != 0.f && pcg_in_range(b, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(b, x, y, z));
+    }
+    for (int ch = lane; ch < ((c + 31) & ~31); ch += 32) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            int rj = __shfl_sync(0xffffffffu, row, j);
+            float wj = __shfl_sync(0xffffffffu, w, j);
+            if (rj >= 0 && ch < c) acc += __ldg(feats + (long)rj * c + ch) * wj;
+        }
+        if (ch < c) out[q * c + ch] = acc;
+    }
+}
+
+extern "C" int pcg_features_at(const uint64_t *keys, const int32_t *vals, long cap, const float *feats, int c, int ts,
+                               const float *query, long nq, float *out, void *stream) {
+    if (nq <= 0) return 0;
+    PCG_CHECK_ARG(cap > 0 && (cap & (cap - 1)) == 0, "pcg_features_at: cap=%ld must be a power of two", cap);
+    k_features_at<<<(unsigned)cdiv(nq * 32, 256), 256, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, feats, c, ts,
+                                                                            query, nq, out);
+    PCG_LAUNCHED();
+    return 0;
+}

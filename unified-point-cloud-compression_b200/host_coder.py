@@ -1,0 +1,72 @@
+"""ctypes binding of libpcg_host.so: host range coder + CDF-table builder (csrc/host_rans.cpp).
+
+The coder stays on the host by design (north-star); it consumes the int32 symbol / index buffers the
+GPU kernels produce (one pinned D2H copy instead of the reference's `.tolist()`).
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpcg_host.so")
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build()")
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.pcg_rans_encode.restype = ctypes.c_long
+        lib.pcg_rans_encode.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_int,
+                                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+        lib.pcg_rans_decode.restype = ctypes.c_int
+        lib.pcg_rans_decode.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p,
+                                        ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.pcg_pmf_to_quantized_cdf.restype = ctypes.c_int
+        lib.pcg_pmf_to_quantized_cdf.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        _lib = lib
+    return _lib
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def encode(symbols, indexes, cdfs, cdf_sizes, offsets):
+    symbols, indexes, cdfs, cdf_sizes, offsets = map(_i32, (symbols, indexes, cdfs, cdf_sizes, offsets))
+    n = symbols.size
+    cap = n * 4 + 1024
+    while True:
+        out = np.empty(cap, dtype=np.uint8)
+        nb = load().pcg_rans_encode(symbols.ctypes.data, indexes.ctypes.data, n, cdfs.ctypes.data, cdfs.shape[1],
+                                    cdf_sizes.ctypes.data, offsets.ctypes.data, out.ctypes.data, cap)
+        if nb >= 0:
+            return out[:nb].tobytes()
+        cap = -nb
+
+
+def decode(encoded, indexes, cdfs, cdf_sizes, offsets):
+    indexes, cdfs, cdf_sizes, offsets = map(_i32, (indexes, cdfs, cdf_sizes, offsets))
+    enc = np.frombuffer(encoded, dtype=np.uint8)
+    out = np.empty(indexes.size, dtype=np.int32)
+    rc = load().pcg_rans_decode(enc.ctypes.data, enc.size, indexes.ctypes.data, indexes.size, cdfs.ctypes.data,
+                                cdfs.shape[1], cdf_sizes.ctypes.data, offsets.ctypes.data, out.ctypes.data)
+    if rc != 0:
+        raise ValueError("corrupt range-coder stream")
+    return out
+
+
+def pmf_to_quantized_cdf(pmf, precision=16):
+    pmf = np.ascontiguousarray(pmf, dtype=np.float32)
+    out = np.empty(pmf.size + 1, dtype=np.int32)
+    rc = load().pcg_pmf_to_quantized_cdf(pmf.ctypes.data, pmf.size, precision, out.ctypes.data)
+    if rc == 1:
+        raise ValueError("Invalid `pmf`, non-finite or negative element found")
+    if rc == 2:
+        raise ValueError("Invalid `pmf`: at least one element must have a non-zero probability.")
+    if rc != 0:
+        raise ValueError("pmf_to_quantized_cdf failed")
+    return out

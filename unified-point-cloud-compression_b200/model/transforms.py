@@ -1,0 +1,124 @@
+"""AnalysisTransform / SparseSynthesisTransform -- mirror of /root/reference/model/transforms.py.
+
+Same sub-module names (down_conv_1..3, up_1..3, predict_1..3, color_conv, prune, down_conv) so the
+reference's checkpoints load.  Differences in *how* (not what):
+  * point counts per level come from the coordinate sets (one bincount for batched input) instead of
+    a python loop of `.item()` syncs (transforms.py:47-64);
+  * the ReLU between the two occupancy-head convolutions is fused into the first conv's epilogue;
+  * top-k is a device radix select (no python loop / torch.topk / nonzero, transforms.py:228-254) and
+    the prune uses the mask directly -- the int64-key `torch.isin` of transforms.py:257-282 recomputes
+    exactly that mask;
+  * `down_conv` is only ever used for its output coordinates (transforms.py:219-220, model.py:227-229):
+    `coords_down()` derives them with the stride-coordinates kernel, no convolution.
+"""
+import torch
+import torch.nn as nn
+
+from .. import MinkowskiEngine as ME
+from .. import sparse_ops as so
+from .blocks import MinkowskiGDN
+
+
+def _conv(cin, cout, k, s=1, bias=True):
+    return ME.MinkowskiConvolution(in_channels=cin, out_channels=cout, kernel_size=k, stride=s, bias=bias, dimension=3)
+
+
+def _gen(cin, cout, k=5, s=2):
+    return ME.MinkowskiGenerativeConvolutionTranspose(in_channels=cin, out_channels=cout, kernel_size=k, stride=s,
+                                                      bias=True, dimension=3)
+
+
+def count_per_batch(x):
+    """Number of rows per batch item, as a python list (transforms.py:47-64)."""
+    b = x.C[:, 0]
+    if x.C.shape[0] == 0:
+        return []
+    counts = torch.bincount(b.long())
+    return [int(c) for c in counts.tolist() if c > 0]
+
+
+class AnalysisTransform(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        c_in, n1, n2, n3, n4 = (config[k] for k in ("C_in", "N1", "N2", "N3", "N4"))
+        self.down_conv_1 = nn.Sequential(_conv(c_in, n1, 5, 2), MinkowskiGDN(n1))
+        self.down_conv_2 = nn.Sequential(_conv(n1, n2, 5, 2), MinkowskiGDN(n2))
+        self.down_conv_3 = nn.Sequential(_conv(n2, n3, 5, 2), MinkowskiGDN(n3), _conv(n3, n4, 5, 1))
+
+    count_per_batch = staticmethod(count_per_batch)
+
+    def forward(self, x):
+        k = [count_per_batch(x)]
+        single = len(k[0]) == 1                      # one batch item: level sizes are just row counts
+        x = self.down_conv_1(x)
+        k.append([x.F.shape[0]] if single else count_per_batch(x))
+        x = self.down_conv_2(x)
+        k.append([x.F.shape[0]] if single else count_per_batch(x))
+        x = self.down_conv_3(x)
+        k.reverse()
+        return x, k
+
+
+class SparseSynthesisTransform(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        c_out, n1, n2, n3, n4 = (config[k] for k in ("C_out", "N1", "N2", "N3", "N4"))
+        self.up_1 = nn.Sequential(_conv(n4, n3, 5, 1), MinkowskiGDN(n3, inverse=True), _gen(n3, n2))
+        self.up_2 = nn.Sequential(MinkowskiGDN(n2, inverse=True), _gen(n2, n1))
+        self.up_3 = nn.Sequential(MinkowskiGDN(n1, inverse=True), _gen(n1, n1 // 4))
+        self.color_conv = nn.Sequential(_conv(n1 // 4, c_out, 1, 1))
+        self.predict_1 = nn.Sequential(_conv(n2, n2 // 2, 3), ME.MinkowskiReLU(inplace=False), _conv(n2 // 2, 1, 3))
+        self.predict_2 = nn.Sequential(_conv(n1, n1 // 2, 3), ME.MinkowskiReLU(inplace=False), _conv(n1 // 2, 1, 3))
+        self.predict_3 = nn.Sequential(_conv(n1 // 4, n4 // 8, 3), ME.MinkowskiReLU(inplace=False), _conv(n4 // 8, 1, 3))
+        self.prune = ME.MinkowskiPruning()
+        self.down_conv = ME.MinkowskiConvolution(in_channels=1, out_channels=1, kernel_size=3, stride=2, dimension=3)
+
+    # -- helpers -----------------------------------------------------------------------------
+    @staticmethod
+    def _head(head, x):
+        """conv -> ReLU -> conv with the ReLU folded into the first epilogue (inference path)."""
+        first, last = head[0], head[2]
+        if torch.is_grad_enabled() and x.F.requires_grad:
+            return head(x)
+        h = so.sparse_conv(x.F, x.coord_set, x.coord_set, first.kernel, first.bias, first.kernel_size, False,
+                           act=so.ACT_RELU, packed=first._packed)
+        o = so.sparse_conv(h, x.coord_set, x.coord_set, last.kernel, last.bias, last.kernel_size, False,
+                           packed=last._packed)
+        return ME.SparseTensor(o, _coord_set=x.coord_set)
+
+    @staticmethod
+    def _topk_prediction(prediction, k):
+        return so.topk_mask(prediction.F[:, 0], prediction.C, [int(v) for v in k])
+
+    def _prune_tensor(self, x, mask, n_keep=None):
+        oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
+        return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
+
+    @staticmethod
+    def coords_down(coord_set, times=1):
+        """Output coordinate set of `down_conv` applied `times` times (a6)."""
+        for _ in range(times):
+            coord_set = coord_set.strided(2)
+        return coord_set
+
+    # -- forward -----------------------------------------------------------------------------
+    def forward(self, y, coords=None, k=None):
+        x = y
+        predictions = []
+        for up, head, k_level in ((self.up_1, self.predict_1, k[0]), (self.up_2, self.predict_2, k[1]),
+                                  (self.up_3, self.predict_3, k[2])):
+            x = up(x)
+            pred = self._head(head, x)
+            predictions.append(pred)
+            mask = self._topk_prediction(pred, k_level)
+            n_avail = [x.F.shape[0]] if len(k_level) == 1 else count_per_batch(x)
+            n_keep = sum(min(int(kk), na) for kk, na in zip(k_level, n_avail)) if len(n_avail) == len(k_level) else None
+            x = self._prune_tensor(x, mask, n_keep)
+        x = self.color_conv(x)
+        if coords is None:
+            return x
+        with torch.no_grad():
+            p1 = self.coords_down(coords.coord_set, 1)
+            p2 = self.coords_down(p1, 1)
+            ones = lambda cs: ME.SparseTensor(torch.ones((cs.n, 1), device=cs.coords.device), _coord_set=cs)
+        return x, [ones(p2), ones(p1), coords], predictions

@@ -1,0 +1,337 @@
+"""Functional layer over libpcg.so: coordinate sets, kernel maps, sparse convolution, pruning,
+feature lookup.  Host-side mirror of what MinkowskiEngine's CoordinateManager + pybind functions
+do for the reference; all arithmetic happens in the CUDA kernels.
+"""
+import weakref
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream
+
+ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
+
+_conv_mode = "auto"      # "auto" | "f32" | "tc"
+
+
+def set_conv_mode(mode):
+    """auto: tcgen05 bf16 where the shape allows, fp32 SIMT otherwise; f32 / tc force one path."""
+    global _conv_mode
+    assert mode in ("auto", "f32", "tc")
+    prev, _conv_mode = _conv_mode, mode
+    return prev
+
+
+def get_conv_mode():
+    return _conv_mode
+
+
+# ----------------------------------------------------------------------------- scratch
+_scratch = {}
+
+
+def scratch(nbytes, device):
+    """Per-device growable workspace (stream-ordered reuse on the current stream)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _need_cuda(t, what):
+    if not t.is_cuda:
+        raise RuntimeError(f"{what} must live on a CUDA device: the graft has no CPU path")
+
+
+# ----------------------------------------------------------------------------- coordinate sets
+class CoordSet:
+    """Unique (N,4) int32 coordinates + their GPU hash table + cached derived sets / kernel maps.
+
+    Stands in for one ME coordinate-map key inside a CoordinateManager.
+    """
+
+    def __init__(self, coords, tensor_stride, table=None):
+        _need_cuda(coords, "coordinates")
+        assert coords.dtype == torch.int32 and coords.dim() == 2 and coords.shape[1] == 4
+        self.coords = coords.contiguous()
+        self.n = int(coords.shape[0])
+        self.ts = int(tensor_stride)
+        self._table = table          # (keys, vals, cap)
+        self._strided = {}
+        self._generated = {}
+        self._kmaps = {}
+        self.coords._pcg_coord_set = (weakref.ref(self), self.coords._version)
+
+    # -- hash table --------------------------------------------------------------------------
+    def table(self):
+        if self._table is None:
+            dev = self.coords.device
+            cap = _lib.load().pcg_hash_capacity(max(self.n, 1))
+            keys = torch.empty(cap, dtype=torch.int64, device=dev)
+            vals = torch.empty(cap, dtype=torch.int32, device=dev)
+            call("pcg_hash_build", ptr(self.coords), self.n, ptr(keys), ptr(vals), cap, stream())
+            self._table = (keys, vals, cap)
+        return self._table
+
+    def lookup(self, query):
+        """Row of every query coordinate (int32 (M,4)), -1 when absent."""
+        keys, vals, cap = self.table()
+        query = query.to(torch.int32).contiguous()
+        rows = torch.empty(query.shape[0], dtype=torch.int32, device=query.device)
+        call("pcg_hash_lookup", ptr(keys), ptr(vals), cap, ptr(query), query.shape[0], ptr(rows), stream())
+        return rows
+
+    # -- derived sets ------------------------------------------------------------------------
+    def strided(self, stride):
+        """Coordinates of a stride-`stride` convolution output (first-occurrence order)."""
+        stride = int(stride)
+        if stride == 1:
+            return self
+        hit = self._strided.get(stride)
+        if hit is None:
+            dev = self.coords.device
+            step = stride * self.ts
+            cap = _lib.load().pcg_hash_capacity(max(self.n, 1))
+            keys = torch.empty(cap, dtype=torch.int64, device=dev)
+            vals = torch.empty(cap, dtype=torch.int32, device=dev)
+            out = torch.empty((self.n, 4), dtype=torch.int32, device=dev)
+            cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+            nb = _lib.load().pcg_scratch_bytes(max(self.n, 1))
+            ws = scratch(nb, dev)
+            call("pcg_stride_coords", ptr(self.coords), self.n, step, ptr(keys), ptr(vals), cap, ptr(out), ptr(cnt),
+                 ptr(ws), ws.numel(), stream())
+            n_out = int(cnt.item())
+            hit = CoordSet(out[:n_out], step, table=(keys, vals, cap))
+            self._strided[stride] = hit
+        return hit
+
+    def generated(self, ksize, stride):
+        """Coordinates of a generative transposed convolution (kernel ksize, up-sampling `stride`)."""
+        key = (int(ksize), int(stride))
+        hit = self._generated.get(key)
+        if hit is None:
+            assert self.ts % stride == 0 and self.ts // stride >= 1, "fractional output tensor stride"
+            ts_out = self.ts // stride
+            dev = self.coords.device
+            K = ksize ** 3
+            lib = _lib.load()
+            n_cand = self.n * K
+            # exact for disjoint children (even kernel == stride); a surface estimate otherwise, retried on overflow
+            max_out = n_cand if (ksize == stride or self.n < 4096) else min(n_cand, 40 * self.n)
+            while True:
+                cap = lib.pcg_hash_capacity(max(max_out, 1))
+                keys = torch.empty(cap, dtype=torch.int64, device=dev)
+                vals = torch.empty(cap, dtype=torch.int32, device=dev)
+                out = torch.empty((max(max_out, 1), 4), dtype=torch.int32, device=dev)
+                cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+                ws = scratch(lib.pcg_scratch_bytes(max(n_cand, 1)), dev)
+                call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), ts_out, ptr(keys), ptr(vals), cap,
+                     ptr(out), max_out, ptr(cnt[0:1]), ptr(cnt[1:2]), ptr(ws), ws.numel(), stream())
+                n_out, status = (int(v) for v in cnt.tolist())
+                if status & 2:
+                    raise RuntimeError("generated coordinate outside the 16-bit packing range")
+                if status == 0:
+                    break
+                if max_out >= n_cand:
+                    raise RuntimeError("pcg_generate_coords: table overflow at full capacity")
+                max_out = n_cand
+            hit = CoordSet(out[:n_out], ts_out, table=(keys, vals, cap))
+            self._generated[key] = hit
+        return hit
+
+    # -- kernel maps -------------------------------------------------------------------------
+    def kernel_map(self, out_set, ksize, transposed):
+        """nbr[K][n_out] (rows of THIS set feeding each output row) + per-128-row-tile offset mask."""
+        key = (id(out_set), int(ksize), bool(transposed))
+        hit = self._kmaps.get(key)
+        if hit is None:
+            keys, vals, cap = self.table()
+            dev = self.coords.device
+            K = ksize ** 3
+            ts = out_set.ts if transposed else self.ts
+            nbr = torch.empty((K, max(out_set.n, 1)), dtype=torch.int32, device=dev)
+            tiles = (out_set.n + 127) // 128
+            tmask = torch.empty((max(tiles, 1), 4), dtype=torch.int32, device=dev) if K <= 128 else None
+            call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
+                 int(bool(transposed)), ptr(nbr), ptr(tmask), stream())
+            hit = (nbr, tmask, None if out_set is self else out_set)   # keep out_set alive while cached (id() key)
+            self._kmaps[key] = hit
+        return hit[0], hit[1]
+
+
+def coord_set_of(coords, tensor_stride):
+    """CoordSet already attached to this exact coordinate tensor, if still valid."""
+    tag = getattr(coords, "_pcg_coord_set", None)
+    if tag is None or tag[1] != coords._version:
+        return None
+    cs = tag[0]()
+    if cs is not None and cs.ts == int(tensor_stride) and cs.coords is coords:
+        return cs
+    return None
+
+
+def unique_first(coords):
+    """(unique coords in first-occurrence order, source row index, table) -- ME ctor / sparse_quantize dedupe."""
+    _need_cuda(coords, "coordinates")
+    coords = coords.to(torch.int32).contiguous()
+    n = coords.shape[0]
+    dev = coords.device
+    lib = _lib.load()
+    cap = lib.pcg_hash_capacity(max(n, 1))
+    keys = torch.empty(cap, dtype=torch.int64, device=dev)
+    vals = torch.empty(cap, dtype=torch.int32, device=dev)
+    out = torch.empty((max(n, 1), 4), dtype=torch.int32, device=dev)
+    index = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = scratch(lib.pcg_scratch_bytes(max(n, 1)), dev)
+    call("pcg_unique_first", ptr(coords), n, ptr(keys), ptr(vals), cap, ptr(out), ptr(index), ptr(cnt), ptr(ws),
+         ws.numel(), stream())
+    m = int(cnt.item())
+    return out[:m], index[:m], (keys, vals, cap)
+
+
+def lexsort(coords):
+    """Permutation sorting rows lexicographically by (b,x,y,z) (utils.py:142-187)."""
+    _need_cuda(coords, "coordinates")
+    coords = coords.to(torch.int32).contiguous()
+    n = coords.shape[0]
+    perm = torch.empty(n, dtype=torch.int32, device=coords.device)
+    if n:
+        lib = _lib.load()
+        ws = scratch(lib.pcg_lexsort_scratch_bytes(n), coords.device)
+        call("pcg_lexsort", ptr(coords), n, ptr(perm), ptr(ws), ws.numel(), stream())
+    return perm.long()
+
+
+# ----------------------------------------------------------------------------- features
+def to_bf16(feats):
+    """bf16 shadow of an fp32 feature matrix (cached on the tensor object)."""
+    tag = getattr(feats, "_pcg_bf16", None)
+    if tag is not None and tag[1] == feats._version:
+        return tag[0]
+    f = feats.contiguous()
+    out = torch.empty(f.shape, dtype=torch.bfloat16, device=f.device)
+    call("pcg_f32_to_bf16", ptr(f), ptr(out), f.numel(), stream())
+    feats._pcg_bf16 = (out, feats._version)
+    return out
+
+
+class PackedWeights:
+    """bf16 UMMA operand image of a (K,cin,cout) kernel, rebuilt when the parameter changes."""
+
+    def __init__(self):
+        self.key, self.buf = None, None
+
+    def get(self, w3):
+        key = (w3.data_ptr(), w3._version, tuple(w3.shape))
+        if key != self.key:
+            K, cin, cout = w3.shape
+            nbytes = _lib.load().pcg_packed_weight_bytes(K, cin, cout)
+            buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
+            call("pcg_pack_weights_bf16", ptr(w3.contiguous()), K, cin, cout, ptr(buf), stream())
+            self.key, self.buf = key, buf
+        return self.buf
+
+
+def tc_eligible(K, cin, cout):
+    return cin % 8 == 0 and cin >= 32 and cout % 16 == 0 and 16 <= cout <= 256 and K <= 128
+
+
+def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT_NONE, packed=None, want_bf16=False):
+    """out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); fp32 features in, fp32 out.
+
+    weight: (K,cin,cout) or (cin,cout) for K == 1.  Chooses the tcgen05 bf16 kernel when the
+    shape allows (static rule, never by timing: determinism).
+    """
+    _need_cuda(feats, "features")
+    w3 = weight if weight.dim() == 3 else weight.unsqueeze(0)
+    K, cin, cout = w3.shape
+    assert K == ksize ** 3 and feats.shape[1] == cin, f"kernel {tuple(w3.shape)} vs features {tuple(feats.shape)}"
+    nbr, tmask = in_set.kernel_map(out_set, ksize, transposed)
+    n_out = out_set.n
+    out = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device)
+    b = bias.reshape(-1).contiguous() if bias is not None else None
+    mode = _conv_mode
+    use_tc = mode != "f32" and tc_eligible(K, cin, cout) and tmask is not None
+    if mode == "tc" and not use_tc:
+        raise RuntimeError(f"conv shape K={K} cin={cin} cout={cout} is not tensor-core eligible")
+    if use_tc:
+        fb = to_bf16(feats)
+        wp = (packed or PackedWeights()).get(w3.detach())
+        ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
+        call("pcg_conv_fwd_tc", ptr(fb), feats.shape[0], cin, ptr(nbr), ptr(tmask), K, n_out, ptr(wp), ptr(b), cout,
+             int(act), ptr(out), ptr(ob), stream())
+        if ob is not None:
+            out._pcg_bf16 = (ob, out._version)
+    else:
+        f = feats.contiguous()
+        call("pcg_conv_fwd_f32", ptr(f), f.shape[0], cin, ptr(nbr), K, n_out, ptr(w3.detach().contiguous()), ptr(b),
+             cout, int(act), ptr(out), stream())
+    return out
+
+
+def channelwise_conv(feats, cset, kernel, ksize):
+    nbr, _ = cset.kernel_map(cset, ksize, False)
+    f = feats.contiguous()
+    out = torch.empty_like(f)
+    k = kernel.detach().contiguous()
+    call("pcg_channelwise_conv", ptr(f), f.shape[1], ptr(nbr), ksize ** 3, cset.n, ptr(k), k.shape[1], ptr(out), stream())
+    return out
+
+
+def activation(feats, act):
+    f = feats.contiguous()
+    out = torch.empty_like(f)
+    call("pcg_activation", ptr(f), f.numel(), int(act), ptr(out), stream())
+    return out
+
+
+def gdn(feats, beta, gamma, inverse):
+    f = feats.contiguous()
+    out = torch.empty_like(f)
+    call("pcg_gdn_fwd", ptr(f), f.shape[0], f.shape[1], ptr(beta.detach().contiguous()), ptr(gamma.detach().contiguous()),
+         int(bool(inverse)), ptr(out), stream())
+    return out
+
+
+def topk_mask(logits, coords, k_per_batch):
+    """Bool mask of the k largest logits per batch item (transforms.py:228-254)."""
+    lg = logits.reshape(-1).contiguous()
+    n = lg.shape[0]
+    mask = torch.zeros(n, dtype=torch.uint8, device=lg.device)
+    if n == 0:
+        return mask.bool()
+    lib = _lib.load()
+    ws = scratch(lib.pcg_scratch_bytes(n), lg.device)
+    for b, k in enumerate(k_per_batch):
+        call("pcg_topk_mask", ptr(lg), ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
+    return mask.bool()
+
+
+def prune_rows(coords, feats, mask, n_keep=None):
+    """Order-preserving compaction of (coords, feats) under a bool mask (ME.MinkowskiPruning)."""
+    n = mask.shape[0]
+    dev = mask.device
+    m8 = mask.to(torch.uint8).contiguous()
+    lib = _lib.load()
+    ws = scratch(lib.pcg_scratch_bytes(max(n, 1)) + 4 * max(n, 1), dev)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    # size unknown: count first (one sync), then compact into exact buffers
+    bound = int(m8.sum().item()) if n_keep is None else int(n_keep)
+    oc = torch.empty((bound, 4), dtype=torch.int32, device=dev) if coords is not None else None
+    of = torch.empty((bound, feats.shape[1]), dtype=torch.float32, device=dev) if feats is not None else None
+    call("pcg_prune_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, n,
+         feats.shape[1] if feats is not None else 0, ptr(m8), ptr(oc), ptr(of), ptr(cnt), ptr(ws), ws.numel(), stream())
+    return oc, of
+
+
+def features_at(feats, cset, query):
+    """Trilinear feature lookup at float query coordinates (N,4) (ME features_at_coordinates)."""
+    keys, vals, cap = cset.table()
+    q = query.to(device=feats.device, dtype=torch.float32).contiguous()
+    f = feats.contiguous()
+    out = torch.empty((q.shape[0], f.shape[1]), dtype=torch.float32, device=f.device)
+    call("pcg_features_at", ptr(keys), ptr(vals), cap, ptr(f), f.shape[1], cset.ts, ptr(q), q.shape[0], ptr(out), stream())
+    return out
