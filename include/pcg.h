@@ -68,24 +68,32 @@ int pcg_stride_coords(const int32_t *coords, long n, int step, uint64_t *keys, i
                       void *stream);
 
 /* Generative up-sampling coordinates unique{p + off_i*ts_out} over all rows and all ksize^3
- * offsets, first-occurrence order (row major, offset minor) + their hash table
+ * offsets + their hash table.  Row order: first occurrence in an enumeration that groups the offsets by
+ * their residue class modulo `stride` (the child's parity class for stride 2), classes ascending, and
+ * inside a class input-row major / offset minor -- the SET equals ME's, the order is chosen so that a
+ * 128-row tile of the following convolution touches one class only
  * (ME CoordinateMapGPU::stride_region; MinkowskiGenerativeConvolutionTranspose, ME3).
  * out_coords must hold max_out rows; *d_n_out > max_out or a full table sets d_status[0]=1. */
-int pcg_generate_coords(const int32_t *coords, long n, int ksize, int ts_out, uint64_t *keys, int32_t *vals,
-                        long cap, int32_t *out_coords, long max_out, int32_t *d_n_out, int32_t *d_status,
-                        void *scratch, size_t scratch_bytes, void *stream);
+int pcg_generate_coords(const int32_t *coords, long n, int ksize, int stride, int ts_out, uint64_t *keys,
+                        int32_t *vals, long cap, int32_t *out_coords, long max_out, int32_t *d_n_out,
+                        int32_t *d_status, void *scratch, size_t scratch_bytes, void *stream);
 
 /* Kernel map (ME CoordinateMapGPU::kernel_map): nbr[i][o] = row of (out_coords[o] +/- off_i*ts)
  * in the table of the INPUT coordinates.  transposed=0: in = out + off*ts (ts = input stride);
  * transposed=1: in = out - off*ts (ts = output stride).  tile_mask (optional, may be NULL):
  * uint32 [ceil(n_out/128)][4], bit i set when any row of the 128-row tile has a neighbour at
- * offset i (ksize^3 <= 128 only). */
+ * offset i (ksize^3 <= 128 only).  in_lattice > 1 declares that input coordinates are multiples of
+ * in_lattice (transposed conv: the input tensor stride), letting impossible offsets skip the probe. */
 int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
-                   int ksize, int ts, int transposed, int32_t *nbr, uint32_t *tile_mask, void *stream);
+                   int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, uint32_t *tile_mask,
+                   void *stream);
 
-/* Lexicographic (b,x,y,z) sort permutation: utils.py:142-187 sort_tensor / sort_points (a11). */
-int pcg_lexsort(const int32_t *coords, long n, int32_t *perm, void *scratch, size_t scratch_bytes, void *stream);
-size_t pcg_lexsort_scratch_bytes(long n);
+/* Row sort permutation.  morton=0: lexicographic (b,x,y,z) -- utils.py:142-187 sort_tensor / sort_points
+ * (a11), the order that defines the bitstream's symbol order.  morton=1: (b, Z-order of x,y,z) -- used once
+ * per block at the codec's entry so that every derived row order is spatially coherent. */
+int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t *perm, void *scratch, size_t scratch_bytes,
+                  void *stream);
+size_t pcg_sort_rows_scratch_bytes(long n);
 
 /* ---- sparse convolution: replaces ME ConvolutionForwardGPU / ConvolutionTransposeForwardGPU
  * (ME2-ME4).  out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); accumulation order is fixed
@@ -93,8 +101,8 @@ size_t pcg_lexsort_scratch_bytes(long n);
 int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, int K, long n_out,
                      const float *weight, const float *bias, int cout, int act, float *out, void *stream);
 
-/* bf16 tensor-core path (tcgen05, fp32 accumulation in TMEM).  cin % 64 == 0,
- * cout % 16 == 0, 16 <= cout <= 256, K <= 128.  feats_bf16: N_in x cin bf16 rows;
+/* bf16 tensor-core path (tcgen05, fp32 accumulation in TMEM).  cin % 8 == 0 (zero-padded to 64-wide
+ * K chunks), cout % 16 == 0, 16 <= cout <= 256, K <= 128.  feats_bf16: N_in x cin bf16 rows;
  * wpacked from pcg_pack_weights_bf16; out_f32 and/or out_bf16 may be NULL. */
 size_t pcg_packed_weight_bytes(int K, int cin, int cout);
 int pcg_pack_weights_bf16(const float *weight, int K, int cin, int cout, void *wpacked, void *stream);

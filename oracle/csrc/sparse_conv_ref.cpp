@@ -142,40 +142,48 @@ void ref_kernel_map(const int32_t *Cin, long n_in, const int32_t *Cout, long n_o
 }
 
 // out[n_out][cout] = bias + sum_k scatter( gather(F, in_k) @ W[k] )   (fp32, ME CPU algorithm)
-// act: 0 none, 1 relu, 2 leaky-relu(0.01)
+// act: 0 none, 1 relu, 2 leaky-relu(0.01).
+// Threading: ME runs the offsets one after another and leaves the threading to OpenBLAS, which does not pay
+// for the small per-offset GEMMs; to give the CPU baseline every core, output rows are split into blocks and
+// each OpenMP thread runs the whole gather -> sgemm -> scatter-add sequence for its block with a
+// single-threaded sgemm (callers set the BLAS thread count to 1).  Per-row arithmetic order is unchanged.
 int ref_conv(const float *F, long n_in, int cin, const int32_t *nbr, int K, long n_out, const float *W,
              const float *bias, int cout, int act, float *out) {
     if (!g_sgemm) return 1;
-#pragma omp parallel for schedule(static)
-    for (long o = 0; o < n_out; ++o)
-        for (int c = 0; c < cout; ++c) out[o * cout + c] = bias ? bias[c] : 0.f;
-    std::vector<int32_t> in_rows, out_rows;
-    std::vector<float> A, Y;
-    for (int k = 0; k < K; ++k) {
-        const int32_t *row = nbr + (long)k * n_out;
-        in_rows.clear(); out_rows.clear();
-        for (long o = 0; o < n_out; ++o)
-            if (row[o] >= 0) { in_rows.push_back(row[o]); out_rows.push_back((int32_t)o); }
-        long P = (long)in_rows.size();
-        if (P == 0) continue;
-        A.resize((size_t)P * cin); Y.resize((size_t)P * cout);
-#pragma omp parallel for schedule(static)
-        for (long p = 0; p < P; ++p) memcpy(&A[(size_t)p * cin], F + (size_t)in_rows[p] * cin, sizeof(float) * cin);
-        g_sgemm(101 /*RowMajor*/, 111, 111, (int)P, cout, cin, 1.f, A.data(), cin, W + (size_t)k * cin * cout, cout, 0.f,
-                Y.data(), cout);
-        // out rows are unique inside one offset -> race-free parallel scatter
-#pragma omp parallel for schedule(static)
-        for (long p = 0; p < P; ++p) {
-            float *dst = out + (size_t)out_rows[p] * cout;
-            const float *src = &Y[(size_t)p * cout];
-            for (int c = 0; c < cout; ++c) dst[c] += src[c];
-        }
-    }
-    if (act) {
-#pragma omp parallel for schedule(static)
-        for (long i = 0; i < n_out * (long)cout; ++i) {
-            float v = out[i];
-            out[i] = v > 0.f ? v : (act == 1 ? 0.f : 0.01f * v);
+    (void)n_in;
+    const long BLK = 2048;
+    const long n_blocks = (n_out + BLK - 1) / BLK;
+#pragma omp parallel
+    {
+        std::vector<int32_t> in_rows, out_rows;
+        std::vector<float> A, Y;
+#pragma omp for schedule(dynamic, 1)
+        for (long blk = 0; blk < n_blocks; ++blk) {
+            const long o0 = blk * BLK, o1 = std::min(n_out, o0 + BLK);
+            for (long o = o0; o < o1; ++o)
+                for (int c = 0; c < cout; ++c) out[o * cout + c] = bias ? bias[c] : 0.f;
+            for (int k = 0; k < K; ++k) {
+                const int32_t *row = nbr + (long)k * n_out;
+                in_rows.clear(); out_rows.clear();
+                for (long o = o0; o < o1; ++o)
+                    if (row[o] >= 0) { in_rows.push_back(row[o]); out_rows.push_back((int32_t)o); }
+                const long P = (long)in_rows.size();
+                if (P == 0) continue;
+                A.resize((size_t)P * cin); Y.resize((size_t)P * cout);
+                for (long p = 0; p < P; ++p) memcpy(&A[(size_t)p * cin], F + (size_t)in_rows[p] * cin, sizeof(float) * cin);
+                g_sgemm(101 /*RowMajor*/, 111, 111, (int)P, cout, cin, 1.f, A.data(), cin, W + (size_t)k * cin * cout, cout,
+                        0.f, Y.data(), cout);
+                for (long p = 0; p < P; ++p) {
+                    float *dst = out + (size_t)out_rows[p] * cout;
+                    const float *src = &Y[(size_t)p * cout];
+                    for (int c = 0; c < cout; ++c) dst[c] += src[c];
+                }
+            }
+            if (act)
+                for (long i = o0 * cout; i < o1 * (long)cout; ++i) {
+                    float v = out[i];
+                    out[i] = v > 0.f ? v : (act == 1 ? 0.f : 0.01f * v);
+                }
         }
     }
     return 0;

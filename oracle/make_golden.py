@@ -38,6 +38,9 @@ def spread_weights(net):
         net.entropy_model.h_a[4].kernel.mul_(30.0)
         net.entropy_model.h_s[4].kernel.mul_(8.0)
         net.entropy_model.h_s[4].bias.add_(0.5)
+        for head in (net.g_s.predict_1, net.g_s.predict_2, net.g_s.predict_3):
+            head[0].bias.add_(0.3)          # keep the (few) hidden channels of the occupancy heads alive past the ReLU
+            head[2].kernel.mul_(20.0)       # and the logits well separated
     net.update()
 
 

@@ -34,9 +34,12 @@ def L():
 
 
 def set_threads(n):
-    L_ = _lib
-    _blas.scipy_openblas_set_num_threads(int(n))
-    L_.ref_set_threads(int(n))
+    if _lib is None:
+        L()
+    # OpenMP owns the cores (row blocks); the per-offset GEMMs are too small for BLAS-level threading and the
+    # two thread pools otherwise fight over the cores (measured: 100x slowdown)
+    _blas.scipy_openblas_set_num_threads(1)
+    _lib.ref_set_threads(int(n))
     return int(n)
 
 

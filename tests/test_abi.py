@@ -44,3 +44,20 @@ def test_cpu_tensors_are_rejected_loudly():
     me = importlib.import_module(pkg.__name__ + ".MinkowskiEngine")
     with pytest.raises(RuntimeError, match="no CPU path"):
         me.SparseTensor(torch.zeros(4, 1), torch.zeros((4, 4), dtype=torch.int32))
+
+
+def test_reference_state_dict_loads_into_product_mirror():
+    """Checkpoint compatibility: the golden state dict was saved by the reference's own UnifiedModel."""
+    import torch
+    from tests.helpers import golden_config, load_golden
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    z, sd = load_golden("ref_inverse_scaling")
+    net = model_mod.UnifiedModel(golden_config(z))
+    missing, unexpected = net.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    assert net.entropy_model.gaussian_conditional._quantized_cdf.shape == sd["entropy_model.gaussian_conditional._quantized_cdf"].shape
+    net.update()        # host-side table rebuild must reproduce the reference's tables exactly
+    assert torch.equal(net.entropy_model.gaussian_conditional._quantized_cdf, sd["entropy_model.gaussian_conditional._quantized_cdf"])
+    assert torch.equal(net.entropy_model.entropy_bottleneck._quantized_cdf, sd["entropy_model.entropy_bottleneck._quantized_cdf"])
+    assert torch.equal(net.entropy_model.entropy_bottleneck._offset, sd["entropy_model.entropy_bottleneck._offset"])

@@ -1,0 +1,128 @@
+"""CUDA sparse convolution (fp32 SIMT and tcgen05 bf16) vs the fp32 oracle, on identical inputs.
+Tolerances (north-star): fp32 path 1e-5 relative L2; bf16 tensor-core path 1e-2 relative L2."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import me_ref, native, synth
+from tests.helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(dev, pkg, seed, ts=1, scale=1):
+    pts, _ = synth.small_cloud(seed=seed, radius=9.0 * scale, centre=(16 * scale,) * 3, n_samples=6000 * scale * scale)
+    C = np.concatenate([np.zeros((len(pts), 1), np.int32), pts * ts], axis=1)
+    cs = pkg.sparse_ops.CoordSet(torch.from_numpy(C).to(dev), ts)
+    return C, cs
+
+
+def oracle_conv(C_in, C_out, Fm, W, b, ksize, ts, transposed, act=0):
+    nbr = native.kernel_map(C_in, C_out, ksize, ts, transposed)
+    return native.conv(Fm, nbr, W, b, act)
+
+
+SHAPES = [  # (cin, cout, ksize, stride, transposed)
+    (4, 128, 5, 2, False), (128, 128, 5, 2, False), (128, 128, 5, 1, False), (128, 64, 3, 1, False),
+    (64, 1, 3, 1, False), (32, 16, 3, 1, False), (16, 1, 3, 1, False), (32, 3, 1, 1, False),
+    (128, 192, 3, 1, False), (192, 192, 3, 2, False), (192, 256, 3, 1, False), (1, 1, 3, 2, False),
+    (192, 192, 2, 2, True), (128, 128, 5, 2, True), (128, 32, 5, 2, True), (3, 5, 3, 1, False), (40, 48, 3, 1, False),
+]
+
+
+@pytest.mark.parametrize("cin,cout,ksize,stride,transposed", SHAPES)
+def test_conv_matches_oracle(pkg, dev, cin, cout, ksize, stride, transposed):
+    so = pkg.sparse_ops
+    ts = 2 if transposed else 1
+    C, cs = setup(dev, pkg, seed=cin + cout, ts=ts)
+    out_set = cs.generated(ksize, stride) if transposed else cs.strided(stride)
+    C_out = out_set.coords.cpu().numpy()
+    rng = np.random.default_rng(cin * 7 + cout)
+    Fm = rng.standard_normal((len(C), cin)).astype(np.float32)
+    K = ksize ** 3
+    W = (rng.standard_normal((K, cin, cout)) / np.sqrt(cin * K) * 3).astype(np.float32)
+    b = rng.standard_normal((1, cout)).astype(np.float32)
+    ref = oracle_conv(C, C_out, Fm, W, b, ksize, (ts // stride) if transposed else ts, transposed, act=1)
+    Wt = torch.from_numpy(W if K > 1 else W[0]).to(dev)
+    modes = [("f32", 2e-5)]
+    if so.tc_eligible(K, cin, cout):
+        modes.append(("tc", 1e-2))
+    for mode, tol in modes:
+        prev = so.set_conv_mode(mode)
+        try:
+            out = so.sparse_conv(torch.from_numpy(Fm).to(dev), cs, out_set, Wt, torch.from_numpy(b).to(dev), ksize,
+                                 transposed, act=so.ACT_RELU)
+        finally:
+            so.set_conv_mode(prev)
+        err = rel_l2(out.cpu().numpy(), ref)
+        assert err < tol, f"{mode}: rel-L2 {err:.3e}"
+
+
+def test_tc_path_is_exact_on_bf16_representable_inputs(pkg, dev):
+    """Integer-valued operands are exact in bf16 and the sums exact in fp32: the tensor-core path must then
+    agree with the fp32 oracle bit for bit (pins operand layout / descriptors, not just a tolerance)."""
+    so = pkg.sparse_ops
+    C, cs = setup(dev, pkg, seed=11)
+    rng = np.random.default_rng(0)
+    for cin, cout, ksize in ((64, 32, 3), (128, 128, 3), (192, 256, 3), (32, 16, 3)):
+        Fm = rng.integers(-4, 5, (len(C), cin)).astype(np.float32)
+        W = rng.integers(-2, 3, (ksize ** 3, cin, cout)).astype(np.float32)
+        b = rng.integers(-3, 4, (1, cout)).astype(np.float32)
+        ref = oracle_conv(C, C, Fm, W, b, ksize, 1, False)
+        prev = so.set_conv_mode("tc")
+        try:
+            out = so.sparse_conv(torch.from_numpy(Fm).to(dev), cs, cs, torch.from_numpy(W).to(dev),
+                                 torch.from_numpy(b).to(dev), ksize, False)
+        finally:
+            so.set_conv_mode(prev)
+        assert np.array_equal(out.cpu().numpy(), ref), f"cin={cin} cout={cout}: max |d| = {np.abs(out.cpu().numpy() - ref).max()}"
+
+
+@pytest.mark.parametrize("mode", ["f32", "tc"])
+def test_conv_is_run_to_run_and_order_deterministic(pkg, dev, mode):
+    """Fact 9: encoder and decoder must reproduce h_s bit-for-bit.  Same inputs -> same bits; and a row's result
+    does not depend on which rows share its tile (permute the rows, compare coordinate-keyed)."""
+    so = pkg.sparse_ops
+    C, cs = setup(dev, pkg, seed=5)
+    rng = np.random.default_rng(1)
+    cin, cout = 64, 64
+    Fm = torch.from_numpy(rng.standard_normal((len(C), cin)).astype(np.float32)).to(dev)
+    W = torch.from_numpy((rng.standard_normal((27, cin, cout)) * 0.1).astype(np.float32)).to(dev)
+    prev = so.set_conv_mode(mode)
+    try:
+        a = so.sparse_conv(Fm, cs, cs, W, None, 3, False)
+        b = so.sparse_conv(Fm, cs, cs, W, None, 3, False)
+        perm = torch.from_numpy(rng.permutation(len(C))).to(dev)
+        cs2 = so.CoordSet(cs.coords[perm].contiguous(), 1)
+        c = so.sparse_conv(Fm[perm].contiguous(), cs2, cs2, W, None, 3, False)
+    finally:
+        so.set_conv_mode(prev)
+    assert torch.equal(a, b)
+    assert torch.equal(a[perm], c)
+
+
+def test_gdn_matches_reference_expression(pkg, dev):
+    so = pkg.sparse_ops
+    torch.manual_seed(0)
+    for n, c in ((1000, 128), (77, 32), (5, 8)):
+        x = torch.randn(n, c)
+        beta = torch.rand(c) + 0.5
+        gamma = torch.rand(c, c) * 0.1
+        norm = torch.nn.functional.conv1d(torch.abs(x.T.unsqueeze(0)), gamma.reshape(c, c, 1), beta)[0].T
+        for inverse in (False, True):
+            ref = x * norm if inverse else x * (1.0 / norm)
+            out = so.gdn(x.to(dev), beta.to(dev), gamma.to(dev), inverse).cpu()
+            assert rel_l2(out.numpy(), ref.numpy()) < 1e-5
+
+
+def test_channelwise_conv_k9(pkg, dev):
+    so = pkg.sparse_ops
+    C = synth.random_cloud(3, 700, 14)
+    cs = so.CoordSet(torch.from_numpy(C).to(dev), 1)
+    Fm = torch.randn(len(C), 4)
+    w = torch.rand(729, 1)
+    mod = me_ref.MinkowskiChannelwiseConvolution(4, kernel_size=9, dimension=3)
+    mod.kernel = torch.nn.Parameter(w)
+    ref = mod(me_ref.SparseTensor(Fm, torch.from_numpy(C))).F.detach()
+    out = so.channelwise_conv(Fm.to(dev), cs, w.to(dev), 9).cpu()
+    assert rel_l2(out.numpy(), ref.numpy()) < 1e-5

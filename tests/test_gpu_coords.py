@@ -1,0 +1,186 @@
+"""CUDA coordinate kernels vs the oracle: bit-exact rows, order included (first-occurrence order == ME CPU)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import me_ref, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def cloud(seed=0, batch=1, n=3000, extent=40):
+    return synth.random_cloud(seed, n, extent, batch=batch)
+
+
+def to_dev(C, dev):
+    return torch.from_numpy(np.ascontiguousarray(C, dtype=np.int32)).to(dev)
+
+
+def test_hash_lookup_and_duplicates(pkg, dev):
+    so = pkg.sparse_ops
+    C = cloud(1, batch=2)
+    dup = np.concatenate([C, C[::3]], axis=0)
+    uniq, index, _ = so.unique_first(to_dev(dup, dev))
+    first = me_ref.unique_first(dup)
+    assert (uniq.cpu().numpy() == dup[first]).all() and (index.cpu().numpy() == first).all()
+    cs = so.CoordSet(to_dev(C, dev), 1)
+    q = np.concatenate([C[::7], C[::11] + np.array([0, 100, 0, 0])], axis=0)
+    rows = cs.lookup(to_dev(q, dev)).cpu().numpy()
+    assert (rows == me_ref._Lookup(C)(q)).all()
+
+
+def test_empty_and_single(pkg, dev):
+    so = pkg.sparse_ops
+    e = so.CoordSet(torch.zeros((0, 4), dtype=torch.int32, device=dev), 1)
+    assert e.strided(2).n == 0
+    one = so.CoordSet(to_dev(np.array([[0, -3, 5, 7]]), dev), 1)
+    assert one.strided(2).coords.cpu().tolist() == [[0, -4, 4, 6]]          # floor for negative coordinates
+    assert one.generated(2, 1).n == 8
+
+
+@pytest.mark.parametrize("ts,stride", [(1, 2), (2, 2), (8, 2), (1, 4)])
+def test_stride_coords(pkg, dev, ts, stride):
+    so = pkg.sparse_ops
+    C = cloud(2, batch=2)
+    C[:, 1:] = (C[:, 1:] - 7) * ts           # include negatives
+    C = C[me_ref.unique_first(C)]
+    out = so.CoordSet(to_dev(C, dev), ts).strided(stride)
+    ref = me_ref.stride_coords(C, ts, stride)
+    assert out.ts == ts * stride and (out.coords.cpu().numpy() == ref).all()
+    # the derived table maps every output coordinate to its own row
+    assert (out.lookup(out.coords).cpu().numpy() == np.arange(len(ref))).all()
+
+
+@pytest.mark.parametrize("ksize,stride", [(2, 2), (5, 2), (3, 1)])
+def test_generate_coords(pkg, dev, ksize, stride):
+    so = pkg.sparse_ops
+    pts, _ = synth.small_cloud(seed=3)
+    C = np.concatenate([np.zeros((len(pts), 1), np.int32), pts * 2], axis=1)
+    out = so.CoordSet(to_dev(C, dev), 2).generated(ksize, stride)
+    ref = me_ref.generate_coords(C, 2 // stride, ksize)
+    got = out.coords.cpu().numpy()
+    # the SET is ME's; the row order is libpcg's own (grouped by child parity class, pcg.h)
+    assert out.n == len(ref) and (np.sort(me_ref.pack_keys(got)) == np.sort(me_ref.pack_keys(ref))).all()
+    assert len(np.unique(me_ref.pack_keys(got))) == len(got)
+    ts_out = 2 // stride
+    cls = ((got[:, 1] // ts_out) % stride * stride + (got[:, 2] // ts_out) % stride) * stride + (got[:, 3] // ts_out) % stride
+    # classes are numbered by the offset residue; parents sit on multiples of `stride`, so the child's residue equals it
+    assert (np.diff(cls) >= 0).all(), "rows must be grouped by parity class, classes ascending"
+    assert (out.lookup(out.coords).cpu().numpy() == np.arange(len(ref))).all()
+
+
+@pytest.mark.parametrize("ksize,ts,stride,transposed", [(3, 1, 1, False), (5, 1, 2, False), (5, 2, 2, False),
+                                                        (2, 2, 2, True), (5, 2, 2, True), (1, 1, 1, False)])
+def test_kernel_map(pkg, dev, ksize, ts, stride, transposed):
+    so = pkg.sparse_ops
+    pts, _ = synth.small_cloud(seed=4)
+    C = np.concatenate([np.zeros((len(pts), 1), np.int32), pts * ts], axis=1)
+    cs = so.CoordSet(to_dev(C, dev), ts)
+    if transposed:
+        out = cs.generated(ksize, stride)
+        ref = me_ref.neighbour_table(C, out.coords.cpu().numpy(), ksize, ts // stride, True)
+    else:
+        out = cs.strided(stride)
+        ref = me_ref.neighbour_table(C, out.coords.cpu().numpy(), ksize, ts, False)
+    nbr, tmask = cs.kernel_map(out, ksize, transposed)
+    assert (nbr.cpu().numpy() == ref).all()
+    if transposed:
+        assert (ref >= 0).sum() == len(C) * ksize ** 3          # every (input, offset) pair lands exactly once
+    tm = tmask.cpu().numpy().view(np.uint32)
+    for t in range(tm.shape[0]):
+        any_k = (ref[:, t * 128:(t + 1) * 128] >= 0).any(axis=1)
+        bits = np.array([(tm[t, k >> 5] >> (k & 31)) & 1 for k in range(ksize ** 3)], bool)
+        assert (bits == any_k).all()
+
+
+def test_kernel_map_k9_no_tile_mask(pkg, dev):
+    so = pkg.sparse_ops
+    C = cloud(5, n=500, extent=14)
+    cs = so.CoordSet(to_dev(C, dev), 1)
+    nbr, tmask = cs.kernel_map(cs, 9, False)
+    assert tmask is None and (nbr.cpu().numpy() == me_ref.neighbour_table(C, C, 9, 1)).all()
+
+
+def test_morton_sort(pkg, dev):
+    so = pkg.sparse_ops
+    C = cloud(9, batch=2)
+    C[:, 1:] -= 13
+    perm = so.sort_rows(to_dev(C, dev), morton=True).cpu().numpy()
+
+    def spread(v):
+        out = np.zeros(len(v), np.uint64)
+        for b in range(16):
+            out |= ((v.astype(np.uint64) >> np.uint64(b)) & np.uint64(1)) << np.uint64(3 * b)
+        return out
+    key = (C[:, 0].astype(np.uint64) << np.uint64(48)) | (spread(C[:, 1] + 32768) << np.uint64(2)) | (spread(C[:, 2] + 32768) << np.uint64(1)) | spread(C[:, 3] + 32768)
+    assert (perm == np.argsort(key, kind="stable")).all()
+
+
+def test_lexsort(pkg, dev):
+    so = pkg.sparse_ops
+    C = cloud(6, batch=3)
+    C[:, 1:] -= 20
+    C = C[np.random.default_rng(0).permutation(len(C))]
+    perm = so.lexsort(to_dev(C, dev)).cpu().numpy()
+    assert (perm == me_ref.lexsort_rows(C)).all()
+
+
+@pytest.mark.parametrize("n,c", [(0, 4), (1, 3), (5000, 128), (4099, 7)])
+def test_prune_rows(pkg, dev, n, c):
+    so = pkg.sparse_ops
+    rng = np.random.default_rng(n)
+    C = rng.integers(0, 100, (n, 4)).astype(np.int32)
+    Fm = rng.standard_normal((n, c)).astype(np.float32)
+    mask = rng.random(n) < 0.3
+    oc, of = so.prune_rows(to_dev(C, dev), torch.from_numpy(Fm).to(dev), torch.from_numpy(mask).to(dev))
+    assert (oc.cpu().numpy() == C[mask]).all() and (of.cpu().numpy() == Fm[mask]).all()
+
+
+@pytest.mark.parametrize("n,k", [(10, 3), (5000, 1234), (5000, 0), (5000, 5000), (5000, 7000), (70000, 35000)])
+def test_topk_mask(pkg, dev, n, k):
+    so = pkg.sparse_ops
+    rng = np.random.default_rng(k + n)
+    logits = rng.standard_normal(n).astype(np.float32)
+    logits[::5] = np.round(logits[::5]) + 0.0        # plenty of exact ties (+0.0: no negative zeros)
+    C = np.zeros((n, 4), np.int32)
+    mask = so.topk_mask(torch.from_numpy(logits).to(dev), to_dev(C, dev), [k]).cpu().numpy()
+    kk = min(k, n)
+    assert mask.sum() == kk
+    if 0 < kk < n:
+        thr = np.sort(logits)[::-1][kk - 1]
+        assert (logits[mask] >= thr).all() and (logits[~mask] <= thr).all()
+        ties = np.nonzero(logits == thr)[0]
+        taken = mask[ties]
+        assert (taken[:taken.sum()]).all()           # ties resolved towards the smaller row index
+
+
+def test_topk_mask_per_batch(pkg, dev):
+    so = pkg.sparse_ops
+    rng = np.random.default_rng(0)
+    n = 6000
+    logits = rng.standard_normal(n).astype(np.float32)
+    C = np.zeros((n, 4), np.int32)
+    C[:, 0] = rng.integers(0, 3, n)
+    ks = [100, 0, 777]
+    mask = so.topk_mask(torch.from_numpy(logits).to(dev), to_dev(C, dev), ks).cpu().numpy()
+    for b, k in enumerate(ks):
+        sel = C[:, 0] == b
+        assert mask[sel].sum() == k
+        if k:
+            assert logits[sel][mask[sel]].min() >= np.sort(logits[sel])[::-1][k - 1]
+
+
+def test_features_at(pkg, dev):
+    so = pkg.sparse_ops
+    C = cloud(7, n=800, extent=10)
+    C[:, 1:] *= 2
+    Fm = torch.randn(len(C), 5)
+    x = me_ref.SparseTensor(Fm, torch.from_numpy(C), tensor_stride=2)
+    rng = np.random.default_rng(1)
+    q_on = np.concatenate([C[::3], C[::5] + np.array([0, 2, 0, 0])]).astype(np.float32)
+    q_off = q_on + rng.uniform(0, 2, q_on.shape).astype(np.float32) * np.array([0, 1, 1, 1], np.float32)
+    cs = so.CoordSet(to_dev(C, dev), 2)
+    for q, tol in ((q_on, 0.0), (q_off, 1e-5)):
+        out = so.features_at(Fm.to(dev), cs, torch.from_numpy(q).to(dev)).cpu()
+        ref = x.features_at_coordinates(torch.from_numpy(q))
+        assert (out - ref).abs().max() <= tol

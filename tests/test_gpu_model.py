@@ -1,0 +1,101 @@
+"""End to end: product host mirror + CUDA kernels vs (a) the committed golden vectors produced by the reference's own
+model/*.py over the oracle and (b) oracle/pipeline_ref.py live."""
+import numpy as np
+import pytest
+import torch
+
+from tests.helpers import (align_rows, build_product_model, golden_config, load_golden, rel_l2, tiny_codec_roundtrip)
+
+pytestmark = pytest.mark.gpu
+
+
+def golden_symbols(z, net):
+    """Symbols the reference run coded, recovered from its strings with the oracle's coder (tables are identical)."""
+    from oracle import rans_ref
+    em = net.entropy_model
+    eb_t = [t.cpu().numpy() for t in (em.entropy_bottleneck._quantized_cdf, em.entropy_bottleneck._cdf_length, em.entropy_bottleneck._offset)]
+    gc_t = [t.cpu().numpy() for t in (em.gaussian_conditional._quantized_cdf, em.gaussian_conditional._cdf_length, em.gaussian_conditional._offset)]
+    return eb_t, gc_t, rans_ref
+
+
+@pytest.mark.parametrize("name", ["ref_inverse_scaling", "ref_inverse_nn", "ref_fixed_R1"])
+def test_compress_decompress_against_reference_golden(pkg, dev, name):
+    z, sd = load_golden(name)
+    net = build_product_model(pkg, golden_config(z), sd, dev)
+    q = torch.from_numpy(z["q"]).reshape(1, 2).to(dev)
+    pc = torch.from_numpy(np.concatenate([z["points"].astype(np.float32), z["colors"]], axis=1)).to(dev)
+    with torch.no_grad():
+        bits, shapes, ks, coords, qv = net.compress(pc, q, block_size=1024)
+    assert [v[0] for v in ks[0]] == z["k"].tolist()
+    assert shapes[0] == z["z_shape"].tolist()
+    # strings: identical unless an fp32 summation-order difference (SIMT fma chain vs OpenBLAS sgemm) moves a value
+    # across a rounding boundary; then at most a handful of symbols differ, by one
+    eb_t, gc_t, rans = golden_symbols(z, net)
+    C = net.entropy_model.entropy_bottleneck.channels
+    nz = int(z["z_shape"][0])
+    z_idx = np.repeat(np.arange(C), nz)
+    mine_z = rans.decode_with_indexes(bits[0][1][0], z_idx, *eb_t)
+    ref_z = rans.decode_with_indexes(z["z_string"].tobytes(), z_idx, *eb_t)
+    assert np.abs(mine_z - ref_z).max() <= 1 and (mine_z != ref_z).mean() <= 0.02
+    if (mine_z == ref_z).all():
+        assert bits[0][1][0] == z["z_string"].tobytes()
+        assert len(bits[0][0][0]) == len(z["y_string"])
+    # decoder fed with the REFERENCE's strings
+    ycoords = torch.from_numpy(z["y_coords"]).to(dev)
+    ref_strings = [[z["y_string"].tobytes()], [z["z_string"].tobytes()]]
+    with torch.no_grad():
+        rec = net.decompress(coordinates=[ycoords], strings=[ref_strings], shape=[z["z_shape"].tolist()], k=ks, q_vals=qv).cpu().numpy()
+    ref = z["reconstruction"]
+    ia, ib = align_rows(rec[:, :3], ref[:, :3])
+    assert len(rec) == len(ref) and len(ia) >= 0.99 * len(ref), f"decoded geometry overlap {len(ia)}/{len(ref)}"
+    assert np.abs(rec[ia, 3:] - ref[ib, 3:]).max() <= 1.0 / 255 + 1e-6
+
+
+def test_eval_forward_against_reference_golden(pkg, dev):
+    import importlib
+    z, sd = load_golden("ref_inverse_scaling")
+    net = build_product_model(pkg, golden_config(z), sd, dev)
+    ME = importlib.import_module(pkg.__name__ + ".MinkowskiEngine")
+    C4 = torch.cat([torch.zeros(len(z["points"]), 1), torch.from_numpy(z["points"]).float()], dim=1)
+    x = ME.SparseTensor(coordinates=C4, features=torch.from_numpy(z["colors"]), device=dev)
+    with torch.no_grad():
+        out = net(x, torch.from_numpy(z["q"]).reshape(1, 2).to(dev), torch.tensor([[1.0, 1.0]], device=dev))
+    assert rel_l2(out["likelihoods"]["z"].cpu().numpy(), z["fwd_lik_z"]) < 1e-2
+    assert rel_l2(out["likelihoods"]["y"].cpu().numpy(), z["fwd_lik_y"]) < 1e-2
+    ia, ib = align_rows(out["occ_predictions"][2].C.cpu().numpy(), z["fwd_occ3_C"])
+    assert len(ia) == len(z["fwd_occ3_C"])
+    assert rel_l2(out["occ_predictions"][2].F.cpu().numpy()[ia], z["fwd_occ3_F"][ib]) < 1e-2
+    ia, ib = align_rows(out["prediction"].C.cpu().numpy(), z["fwd_pred_C"])
+    assert len(ia) >= 0.99 * len(z["fwd_pred_C"])
+    assert rel_l2(out["prediction"].F.cpu().numpy()[ia], z["fwd_pred_F"][ib]) < 1e-2
+
+
+@pytest.mark.parametrize("width,mode", [(32, "f32"), (64, "f32"), (32, "auto"), (64, "auto")])
+def test_codec_roundtrip_vs_oracle_pipeline(pkg, dev, width, mode):
+    stats = tiny_codec_roundtrip(pkg, dev, width=width, mode=mode)
+    print(f"width={width} mode={mode}: {stats}")
+
+
+def test_encoder_decoder_agree_on_indexes_bitwise(pkg, dev):
+    """Two independent runs of the hyper-synthesis path give identical CDF indexes."""
+    import importlib
+    from tests.helpers import model_config, spread_weights
+    from oracle import synth
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    torch.manual_seed(0)
+    net = model_mod.UnifiedModel(model_config(width=64))
+    spread_weights(net)
+    net = net.to(dev).eval()
+    net.update()
+    pts, rgb = synth.small_cloud(seed=3, radius=12.0, centre=(20, 20, 20), n_samples=12000)
+    xb = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).to(dev)
+    q = torch.tensor([[0.3, 0.8]], device=dev)
+    seen = {}
+    with torch.no_grad():
+        enc = net.encode_block(xb, q)
+
+        def grab(idx):
+            seen["idx"] = idx.clone()
+            return enc["y_symbols"]
+        net.decode_block(enc["y_points"], enc["z_symbols"], grab, enc["k"], q)
+    assert torch.equal(seen["idx"].reshape(-1), enc["y_indexes"].reshape(-1))

@@ -25,10 +25,10 @@ _PROTOS = {
     "pcg_hash_lookup": (_I, [_P, _P, _L, _P, _L, _P, _P]),
     "pcg_unique_first": (_I, [_P, _L, _P, _P, _L, _P, _P, _P, _P, _SZ, _P]),
     "pcg_stride_coords": (_I, [_P, _L, _I, _P, _P, _L, _P, _P, _P, _SZ, _P]),
-    "pcg_generate_coords": (_I, [_P, _L, _I, _I, _P, _P, _L, _P, _L, _P, _P, _P, _SZ, _P]),
-    "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _P, _P, _P]),
-    "pcg_lexsort": (_I, [_P, _L, _P, _P, _SZ, _P]),
-    "pcg_lexsort_scratch_bytes": (_SZ, [_L]),
+    "pcg_generate_coords": (_I, [_P, _L, _I, _I, _I, _P, _P, _L, _P, _L, _P, _P, _P, _SZ, _P]),
+    "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _P, _P]),
+    "pcg_sort_rows": (_I, [_P, _L, _I, _P, _P, _SZ, _P]),
+    "pcg_sort_rows_scratch_bytes": (_SZ, [_L]),
     "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _I, _L, _P, _P, _I, _I, _P, _P]),
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),
     "pcg_pack_weights_bf16": (_I, [_P, _I, _I, _I, _P, _P]),

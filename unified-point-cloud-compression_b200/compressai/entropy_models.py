@@ -63,6 +63,16 @@ class EntropyModel(nn.Module):
         self.register_buffer("_cdf_length", torch.IntTensor())
         self._host_tables = None
 
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        # checkpoints carry the CDF buffers at their updated sizes (compressai resizes them in
+        # CompressionModel.load_state_dict / update_registered_buffers): adopt the incoming shapes
+        for name in ("_offset", "_quantized_cdf", "_cdf_length", "scale_table"):
+            src = state_dict.get(prefix + name)
+            cur = getattr(self, name, None)
+            if src is not None and cur is not None and tuple(src.shape) != tuple(cur.shape):
+                setattr(self, name, torch.empty(src.shape, dtype=cur.dtype, device=cur.device))
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
     # -- quantisation --------------------------------------------------------------------------
     def quantize(self, inputs, mode, means=None):
         if mode not in ("noise", "dequantize", "symbols"):
@@ -92,7 +102,7 @@ class EntropyModel(nn.Module):
             prob = torch.cat((p[: pmf_length[i]], tail_mass[i]), dim=0)
             _cdf = torch.from_numpy(host_coder.pmf_to_quantized_cdf(prob.numpy(), self.entropy_coder_precision))
             cdf[i, : _cdf.size(0)] = _cdf
-        return cdf.to(pmf_length.device)
+        return cdf
 
     def _check_cdf_size(self):
         if self._quantized_cdf.numel() == 0:
@@ -175,41 +185,48 @@ class EntropyBottleneck(EntropyModel):
         return self._packed[1]
 
     def update(self, force=False, update_quantiles=False):
+        """Build the 16-bit CDF tables.  Always evaluated on the host in fp32, whatever device the parameters live on:
+        the tables are part of the bitstream contract, and ulp-level differences between a GPU and a CPU evaluation of
+        the pmf would otherwise give encoder and decoder different tables."""
         if self._offset.numel() > 0 and not force:
             return False
-        medians = self.quantiles[:, 0, 1]
-        minima = torch.clamp(torch.ceil(medians - self.quantiles[:, 0, 0]).int(), min=0)
-        maxima = torch.clamp(torch.ceil(self.quantiles[:, 0, 2] - medians).int(), min=0)
-        self._offset = -minima
+        dev = self.quantiles.device
+        quantiles = self.quantiles.detach().cpu()
+        medians = quantiles[:, 0, 1]
+        minima = torch.clamp(torch.ceil(medians - quantiles[:, 0, 0]).int(), min=0)
+        maxima = torch.clamp(torch.ceil(quantiles[:, 0, 2] - medians).int(), min=0)
         pmf_start = medians - minima
         pmf_length = maxima + minima + 1
         max_length = int(pmf_length.max().item())
-        samples = torch.arange(max_length, device=pmf_start.device)[None, :] + pmf_start[:, None, None]
-        pmf, lower, upper = self._likelihood(samples, stop_gradient=True)
+        samples = torch.arange(max_length)[None, :] + pmf_start[:, None, None]
+        host = [[p.detach().cpu() for p in plist] for plist in (self.matrices, self.biases, self.factors)]
+        pmf, lower, upper = self._likelihood(samples, stop_gradient=True, params=host)
         pmf = pmf[:, 0, :]
         tail_mass = torch.sigmoid(lower[:, 0, :1]) + torch.sigmoid(-upper[:, 0, -1:])
-        self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length)
-        self._cdf_length = pmf_length + 2
+        self._offset = (-minima).to(dev)
+        self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length).to(dev)
+        self._cdf_length = (pmf_length + 2).to(dev)
         return True
 
     def loss(self):
         logits = self._logits_cumulative(self.quantiles, stop_gradient=True)
         return torch.abs(logits - self.target).sum()
 
-    def _logits_cumulative(self, inputs, stop_gradient):
+    def _logits_cumulative(self, inputs, stop_gradient, params=None):
+        matrices, biases, factors = params if params is not None else (self.matrices, self.biases, self.factors)
         logits = inputs
         for i in range(len(self.filters) + 1):
-            matrix = self.matrices[i].detach() if stop_gradient else self.matrices[i]
-            bias = self.biases[i].detach() if stop_gradient else self.biases[i]
+            matrix = matrices[i].detach() if stop_gradient else matrices[i]
+            bias = biases[i].detach() if stop_gradient else biases[i]
             logits = torch.matmul(F.softplus(matrix), logits) + bias
             if i < len(self.filters):
-                factor = self.factors[i].detach() if stop_gradient else self.factors[i]
+                factor = factors[i].detach() if stop_gradient else factors[i]
                 logits = logits + torch.tanh(factor) * torch.tanh(logits)
         return logits
 
-    def _likelihood(self, inputs, stop_gradient=False):
-        lower = self._logits_cumulative(inputs - 0.5, stop_gradient)
-        upper = self._logits_cumulative(inputs + 0.5, stop_gradient)
+    def _likelihood(self, inputs, stop_gradient=False, params=None):
+        lower = self._logits_cumulative(inputs - 0.5, stop_gradient, params)
+        upper = self._logits_cumulative(inputs + 0.5, stop_gradient, params)
         return torch.sigmoid(upper) - torch.sigmoid(lower), lower, upper
 
     def _needs_grad(self, x):
@@ -298,20 +315,22 @@ class GaussianConditional(EntropyModel):
         return True
 
     def update(self):
+        """16-bit CDF tables per scale-table entry; evaluated on the host (see EntropyBottleneck.update)."""
+        dev = self.scale_table.device
+        table = self.scale_table.detach().cpu()
         multiplier = -self._standardized_quantile(self.tail_mass / 2)
-        pmf_center = torch.ceil(self.scale_table * multiplier).int()
+        pmf_center = torch.ceil(table * multiplier).int()
         pmf_length = 2 * pmf_center + 1
         max_length = int(torch.max(pmf_length).item())
-        device = pmf_center.device
-        samples = torch.abs(torch.arange(max_length, device=device).int() - pmf_center[:, None]).float()
-        samples_scale = self.scale_table.unsqueeze(1).float()
+        samples = torch.abs(torch.arange(max_length).int() - pmf_center[:, None]).float()
+        samples_scale = table.unsqueeze(1).float()
         upper = self._standardized_cumulative((0.5 - samples) / samples_scale)
         lower = self._standardized_cumulative((-0.5 - samples) / samples_scale)
         pmf = upper - lower
         tail_mass = 2 * lower[:, :1]
-        self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length)
-        self._offset = -pmf_center
-        self._cdf_length = pmf_length + 2
+        self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length).to(dev)
+        self._offset = (-pmf_center).to(dev)
+        self._cdf_length = (pmf_length + 2).to(dev)
 
     def _likelihood(self, inputs, scales, means=None):
         values = inputs - means if means is not None else inputs

@@ -208,19 +208,57 @@ extern "C" int pcg_stride_coords(const int32_t *coords, long n, int step, uint64
 }
 
 // ---------------------------------------------------------------------------- generative coords
+// Candidate enumeration of the generative up-sampling.  Offsets are grouped into classes by their residue
+// modulo the up-sampling stride (for stride 2: the parity class of the child voxel), classes in ascending
+// order, and inside a class candidates run input-row major / offset minor.  Output rows therefore come out
+// grouped by class, so a 128-row tile of the following convolution only ever touches the (k/stride)^3-ish
+// offsets its class can reach instead of all k^3 -- and rows of one tile stem from neighbouring parents.
 struct GenKey {
     const int32_t *coords;
     int ksize, K, ts_out;
+    long n;
+    int n_classes;
+    int cls_count[65];     // offsets per class
+    long cls_base[65];     // first candidate id of the class (= n * offsets in earlier classes)
+    int cls_first[65];     // start of the class in `order16`
+    unsigned short order16[736];   // offset indices sorted by class (stable)
     __device__ __forceinline__ int4 coord(long cand) const {
-        long row = cand / K;
-        int k = (int)(cand - row * K);
-        int4 c = pcg_ld_coord(coords, row);
+        int c = 0;
+        while (c + 1 < n_classes && cand >= cls_base[c + 1]) ++c;
+        long rel = cand - cls_base[c];
+        long row = rel / cls_count[c];
+        int t = (int)(rel - row * cls_count[c]);
+        int4 v = pcg_ld_coord(coords, row);
         int dx, dy, dz;
-        pcg_kernel_offset(k, ksize, dx, dy, dz);
-        c.y += dx * ts_out; c.z += dy * ts_out; c.w += dz * ts_out;
-        return c;
+        pcg_kernel_offset(k_of(cls_first[c] + t), ksize, dx, dy, dz);
+        v.y += dx * ts_out; v.z += dy * ts_out; v.w += dz * ts_out;
+        return v;
     }
+    __device__ __forceinline__ int k_of(int pos) const { return order16[pos]; }
 };
+
+static void gen_key_init(GenKey &g, const int32_t *coords, long n, int ksize, int ts_out, int stride) {
+    g.coords = coords; g.ksize = ksize; g.K = ksize * ksize * ksize; g.ts_out = ts_out; g.n = n;
+    int s = stride < 1 ? 1 : stride;
+    if (s > 4) s = 4;
+    g.n_classes = s * s * s;
+    const int lo = (ksize & 1) ? -(ksize >> 1) : 0;
+    auto md = [s](int v) { int r = v % s; return r < 0 ? r + s : r; };
+    int pos = 0;
+    long base = 0;
+    for (int c = 0; c < g.n_classes; ++c) {
+        g.cls_first[c] = pos;
+        g.cls_base[c] = base;
+        int cnt = 0;
+        for (int k = 0; k < g.K; ++k) {
+            int dx = lo + k % ksize, dy = lo + (k / ksize) % ksize, dz = lo + k / (ksize * ksize);
+            if ((md(dx) * s + md(dy)) * s + md(dz) == c) { g.order16[pos++] = (unsigned short)k; ++cnt; }
+        }
+        g.cls_count[c] = cnt > 0 ? cnt : 1;
+        base += (long)cnt * n;
+    }
+    g.cls_base[g.n_classes] = base;
+}
 
 __global__ void k_insert_generated(GenKey gk, long n_cand, uint64_t *keys, int32_t *vals, uint64_t mask, int32_t *d_status) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -256,9 +294,9 @@ __global__ void k_flag_overflow(const int32_t *d_n_out, long max_out, int32_t *d
     if (d_n_out[0] > max_out) atomicOr(d_status, 1);
 }
 
-extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int ts_out, uint64_t *keys, int32_t *vals,
-                                   long cap, int32_t *out_coords, long max_out, int32_t *d_n_out, int32_t *d_status,
-                                   void *scratch, size_t scratch_bytes, void *stream) {
+extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int stride, int ts_out, uint64_t *keys,
+                                   int32_t *vals, long cap, int32_t *out_coords, long max_out, int32_t *d_n_out,
+                                   int32_t *d_status, void *scratch, size_t scratch_bytes, void *stream) {
     cudaStream_t st = as_stream(stream);
     PCG_CHECK_ARG(ksize >= 1 && ksize <= 9 && ts_out >= 1, "pcg_generate_coords: ksize=%d ts_out=%d", ksize, ts_out);
     int K = ksize * ksize * ksize;
@@ -274,7 +312,8 @@ extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int
         PCG_CUDA(cudaMemsetAsync(d_n_out, 0, sizeof(int32_t), st));
         return 0;
     }
-    GenKey gk{coords, ksize, K, ts_out};
+    GenKey gk;
+    gen_key_init(gk, coords, n, ksize, ts_out, stride);
     uint64_t mask = (uint64_t)cap - 1;
     k_insert_generated<<<(unsigned)cdiv(n_cand, 256), 256, 0, st>>>(gk, n_cand, keys, vals, mask, d_status);
     PCG_LAUNCHED();
@@ -295,7 +334,7 @@ extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int
 // coordinate is loaded once (int4) and nbr[k][tile rows] is written as one coalesced 512 B line.
 __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
                                                     uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
-                                                    int ksize, int K, int step, int32_t *__restrict__ nbr,
+                                                    int ksize, int K, int step, int lattice, int32_t *__restrict__ nbr,
                                                     uint32_t *__restrict__ tile_mask) {
     long o = (long)blockIdx.x * 128 + threadIdx.x;
     bool live = o < n_out;
@@ -311,7 +350,10 @@ __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__
                 int row = -1;
                 if (live) {
                     int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
-                    if (pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
+                    // lattice > 0: input rows only exist on multiples of `lattice` (transposed conv onto a finer
+                    // grid), so most offsets cannot hit for a given output parity -- no probe needed
+                    bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
+                    if (possible && pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
                     nbr[(long)k * n_out + o] = row;
                 }
                 if (tile_mask) {
@@ -326,7 +368,8 @@ __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__
 }
 
 extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
-                              int ksize, int ts, int transposed, int32_t *nbr, uint32_t *tile_mask, void *stream) {
+                              int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, uint32_t *tile_mask,
+                              void *stream) {
     PCG_CHECK_ARG(is_pow2(cap), "pcg_kernel_map: cap=%ld must be a power of two", cap);
     PCG_CHECK_ARG(ksize >= 1 && ksize <= 9 && ts >= 1, "pcg_kernel_map: ksize=%d ts=%d", ksize, ts);
     int K = ksize * ksize * ksize;
@@ -334,7 +377,7 @@ extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long ca
     if (n_out <= 0) return 0;
     int step = transposed ? -ts : ts;
     k_kernel_map<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
-                                                                           ksize, K, step, nbr, tile_mask);
+                                                                           ksize, K, step, in_lattice, nbr, tile_mask);
     PCG_LAUNCHED();
     return 0;
 }
@@ -394,17 +437,32 @@ extern "C" int pcg_prune_rows(const int32_t *coords, const float *feats, long n,
 }
 
 // ---------------------------------------------------------------------------- lexsort
-__global__ void k_pack_keys(const int32_t *__restrict__ coords, long n, uint64_t *keys, int32_t *idx) {
+__device__ __forceinline__ uint64_t spread3(uint32_t v) {   // 16 bits -> every third bit of 48
+    uint64_t x = v & 0xFFFFu;
+    x = (x | (x << 32)) & 0x00FF00000000FFFFull;
+    x = (x | (x << 16)) & 0x00FF0000FF0000FFull;
+    x = (x | (x << 8)) & 0xF00F00F00F00F00Full;
+    x = (x | (x << 4)) & 0x30C30C30C30C30C3ull;
+    x = (x | (x << 2)) & 0x9249249249249249ull;
+    return x;
+}
+
+__global__ void k_pack_keys(const int32_t *__restrict__ coords, long n, int morton, uint64_t *keys, int32_t *idx) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int4 c = pcg_ld_coord(coords, i);
-    keys[i] = pcg_pack(c.x, c.y, c.z, c.w);
+    if (morton) {
+        uint64_t m = (spread3((uint32_t)(c.y + 32768)) << 2) | (spread3((uint32_t)(c.z + 32768)) << 1) | spread3((uint32_t)(c.w + 32768));
+        keys[i] = ((uint64_t)(uint16_t)c.x << 48) | (m & 0xFFFFFFFFFFFFull);
+    } else {
+        keys[i] = pcg_pack(c.x, c.y, c.z, c.w);
+    }
     idx[i] = (int)i;
 }
 
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-extern "C" size_t pcg_lexsort_scratch_bytes(long n) {
+extern "C" size_t pcg_sort_rows_scratch_bytes(long n) {
     size_t temp = 0;
     long m = n > 0 ? n : 1;
     cub::DeviceRadixSort::SortPairs(nullptr, temp, (const uint64_t *)nullptr, (uint64_t *)nullptr, (const int32_t *)nullptr,
@@ -412,16 +470,17 @@ extern "C" size_t pcg_lexsort_scratch_bytes(long n) {
     return align256(temp) + 2 * align256((size_t)m * 8) + align256((size_t)m * 4) + 256;
 }
 
-extern "C" int pcg_lexsort(const int32_t *coords, long n, int32_t *perm, void *scratch, size_t scratch_bytes, void *stream) {
+extern "C" int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t *perm, void *scratch, size_t scratch_bytes,
+                             void *stream) {
     cudaStream_t st = as_stream(stream);
     if (n <= 0) return 0;
-    PCG_CHECK_ARG(scratch && scratch_bytes >= pcg_lexsort_scratch_bytes(n), "pcg_lexsort: scratch too small");
+    PCG_CHECK_ARG(scratch && scratch_bytes >= pcg_sort_rows_scratch_bytes(n), "pcg_sort_rows: scratch too small");
     uint8_t *p = reinterpret_cast<uint8_t *>(scratch);
     uint64_t *k_in = reinterpret_cast<uint64_t *>(p); p += align256((size_t)n * 8);
     uint64_t *k_out = reinterpret_cast<uint64_t *>(p); p += align256((size_t)n * 8);
     int32_t *i_in = reinterpret_cast<int32_t *>(p); p += align256((size_t)n * 4);
     size_t temp = scratch_bytes - (size_t)(p - reinterpret_cast<uint8_t *>(scratch));
-    k_pack_keys<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, k_in, i_in);
+    k_pack_keys<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, morton, k_in, i_in);
     PCG_LAUNCHED();
     // plumbing: CUB's radix sort orders the packed 64-bit keys (stable)
     PCG_CUDA(cub::DeviceRadixSort::SortPairs(p, temp, k_in, k_out, i_in, perm, (int)n, 0, 64, st));

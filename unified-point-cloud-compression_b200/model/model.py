@@ -54,15 +54,21 @@ class UnifiedModel(CompressionModel):
 
     # -- GPU halves --------------------------------------------------------------------------------
     def block_tensor(self, x_block):
-        """(n,6) float [xyz|rgb] rows of one block -> deduplicated SparseTensor with the occupancy channel."""
+        """(n,6) float [xyz|rgb] rows of one block -> deduplicated SparseTensor with the occupancy channel.
+
+        Rows are put in Z-order first: MinkowskiEngine semantics do not depend on row order, and every derived
+        coordinate set (strided / generated, first-occurrence order) inherits the spatial coherence, which is what
+        lets a 128-row convolution tile skip the kernel offsets its surface patch does not use."""
         dev = x_block.device
         coords4 = torch.cat([torch.zeros((x_block.shape[0], 1), dtype=torch.int32, device=dev),
                              torch.floor(x_block[:, :3]).to(torch.int32)], dim=1)
+        order = so.sort_rows(coords4, morton=True)
+        coords4, rgb = coords4[order].contiguous(), x_block[order, 3:6]
         uniq, index, table = so.unique_first(coords4)
-        rgb = x_block[:, 3:6] if uniq.shape[0] == x_block.shape[0] else x_block[index.long(), 3:6]
-        feats = torch.cat([torch.ones((uniq.shape[0], 1), device=dev), rgb], dim=1)
-        cs = so.CoordSet(uniq if uniq.shape[0] != x_block.shape[0] else coords4, 1, table=table)
-        return ME.SparseTensor(feats, _coord_set=cs)
+        if uniq.shape[0] != coords4.shape[0]:
+            coords4, rgb = uniq, rgb[index.long()]
+        feats = torch.cat([torch.ones((coords4.shape[0], 1), device=dev), rgb], dim=1)
+        return ME.SparseTensor(feats, _coord_set=so.CoordSet(coords4, 1, table=table))
 
     def encode_block(self, x_block, q):
         """g_a + hyper-analysis + quantisation + CDF indexes on the GPU; returns device symbol buffers + k."""

@@ -127,7 +127,7 @@ class CoordSet:
                 out = torch.empty((max(max_out, 1), 4), dtype=torch.int32, device=dev)
                 cnt = torch.zeros(2, dtype=torch.int32, device=dev)
                 ws = scratch(lib.pcg_scratch_bytes(max(n_cand, 1)), dev)
-                call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), ts_out, ptr(keys), ptr(vals), cap,
+                call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), int(stride), ts_out, ptr(keys), ptr(vals), cap,
                      ptr(out), max_out, ptr(cnt[0:1]), ptr(cnt[1:2]), ptr(ws), ws.numel(), stream())
                 n_out, status = (int(v) for v in cnt.tolist())
                 if status & 2:
@@ -155,7 +155,7 @@ class CoordSet:
             tiles = (out_set.n + 127) // 128
             tmask = torch.empty((max(tiles, 1), 4), dtype=torch.int32, device=dev) if K <= 128 else None
             call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
-                 int(bool(transposed)), ptr(nbr), ptr(tmask), stream())
+                 int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), ptr(tmask), stream())
             hit = (nbr, tmask, None if out_set is self else out_set)   # keep out_set alive while cached (id() key)
             self._kmaps[key] = hit
         return hit[0], hit[1]
@@ -192,17 +192,21 @@ def unique_first(coords):
     return out[:m], index[:m], (keys, vals, cap)
 
 
-def lexsort(coords):
-    """Permutation sorting rows lexicographically by (b,x,y,z) (utils.py:142-187)."""
+def sort_rows(coords, morton=False):
+    """Row permutation: lexicographic (b,x,y,z) (utils.py:142-187) or, with morton=True, (b, Z-order)."""
     _need_cuda(coords, "coordinates")
     coords = coords.to(torch.int32).contiguous()
     n = coords.shape[0]
     perm = torch.empty(n, dtype=torch.int32, device=coords.device)
     if n:
         lib = _lib.load()
-        ws = scratch(lib.pcg_lexsort_scratch_bytes(n), coords.device)
-        call("pcg_lexsort", ptr(coords), n, ptr(perm), ptr(ws), ws.numel(), stream())
+        ws = scratch(lib.pcg_sort_rows_scratch_bytes(n), coords.device)
+        call("pcg_sort_rows", ptr(coords), n, int(bool(morton)), ptr(perm), ptr(ws), ws.numel(), stream())
     return perm.long()
+
+
+def lexsort(coords):
+    return sort_rows(coords, morton=False)
 
 
 # ----------------------------------------------------------------------------- features
@@ -235,6 +239,35 @@ class PackedWeights:
         return self.buf
 
 
+class ConvProfiler:
+    """Optional per-launch CUDA-event timing of the convolution kernels (bench.py's roofline pass).
+    Events are recorded on torch's current stream, which is the stream the kernels are launched on."""
+
+    def __init__(self):
+        self.records = []
+        self._pairs = {}
+
+    def pairs(self, nbr):
+        key = nbr.data_ptr()
+        if key not in self._pairs:
+            self._pairs[key] = int((nbr >= 0).sum().item())
+        return self._pairs[key]
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for kind, shape, flops, bytes_, e0, e1 in self.records:
+            d = out.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0, "by_shape": {}})
+            ms = e0.elapsed_time(e1)
+            d["launches"] += 1; d["ms"] += ms; d["flops"] += flops; d["bytes"] += bytes_
+            b = d["by_shape"].setdefault(shape, [0, 0.0, 0.0])
+            b[0] += 1; b[1] += ms; b[2] += flops
+        return out
+
+
+profiler = None      # set to a ConvProfiler() to time every convolution launch
+
+
 def tc_eligible(K, cin, cout):
     return cin % 8 == 0 and cin >= 32 and cout % 16 == 0 and 16 <= cout <= 256 and K <= 128
 
@@ -257,18 +290,34 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     use_tc = mode != "f32" and tc_eligible(K, cin, cout) and tmask is not None
     if mode == "tc" and not use_tc:
         raise RuntimeError(f"conv shape K={K} cin={cin} cout={cout} is not tensor-core eligible")
+    prof = profiler
+    if prof is not None:
+        pairs = prof.pairs(nbr)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if use_tc:
         fb = to_bf16(feats)
         wp = (packed or PackedWeights()).get(w3.detach())
         ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
+        if prof is not None:
+            e0.record()
         call("pcg_conv_fwd_tc", ptr(fb), feats.shape[0], cin, ptr(nbr), ptr(tmask), K, n_out, ptr(wp), ptr(b), cout,
              int(act), ptr(out), ptr(ob), stream())
+        if prof is not None:
+            e1.record()
+            prof.records.append(("conv_tc", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                 2.0 * feats.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
         if ob is not None:
             out._pcg_bf16 = (ob, out._version)
     else:
         f = feats.contiguous()
+        if prof is not None:
+            e0.record()
         call("pcg_conv_fwd_f32", ptr(f), f.shape[0], cin, ptr(nbr), K, n_out, ptr(w3.detach().contiguous()), ptr(b),
              cout, int(act), ptr(out), stream())
+        if prof is not None:
+            e1.record()
+            prof.records.append(("conv_f32", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                 4.0 * f.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
     return out
 
 
