@@ -22,8 +22,9 @@
  *   - features are row-major fp32 (N x C) unless a bf16 shadow is named;
  *   - kernel offsets follow MinkowskiEngine: odd k -> {-(k/2)..k/2}, even k -> {0..k-1},
  *     offset index i = ix + k*iy + k*k*iz;
- *   - a neighbour table `nbr` is int32 [K][n_out]: the input row feeding output row o through
- *     kernel offset i, or -1.
+ *   - a neighbour table `nbr` is int32 [K][pitch], pitch = pcg_nbr_pitch(n_out) (n_out rounded up to 128 so
+ *     that every 128-row tile of every kernel offset is one aligned 512-byte line): nbr[i][o] = the input row
+ *     feeding output row o through kernel offset i, or -1; the padding entries are -1.
  */
 #ifndef PCG_H
 #define PCG_H
@@ -45,6 +46,7 @@ long pcg_launch_count(void);
 
 /* ---- scratch sizing (host helpers, no GPU work) ------------------------------------------ */
 long pcg_hash_capacity(long n_keys);            /* power of two >= 2*n_keys (min 1024) */
+long pcg_nbr_pitch(long n_out);                 /* row pitch (elements) of a neighbour table over n_out output rows */
 size_t pcg_scratch_bytes(long n_items);         /* scratch needed by any compaction/select over n_items */
 
 /* ---- coordinate hash: replaces ME CoordinateMapGPU::insert_and_map (ME1) -------------------
@@ -85,7 +87,7 @@ int pcg_generate_coords(const int32_t *coords, long n, int ksize, int stride, in
  * offset i (ksize^3 <= 128 only).  in_lattice > 1 declares that input coordinates are multiples of
  * in_lattice (transposed conv: the input tensor stride), letting impossible offsets skip the probe. */
 int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
-                   int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, uint32_t *tile_mask,
+                   int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, long nbr_pitch, uint32_t *tile_mask,
                    void *stream);
 
 /* Row sort permutation.  morton=0: lexicographic (b,x,y,z) -- utils.py:142-187 sort_tensor / sort_points
@@ -98,23 +100,29 @@ size_t pcg_sort_rows_scratch_bytes(long n);
 /* ---- sparse convolution: replaces ME ConvolutionForwardGPU / ConvolutionTransposeForwardGPU
  * (ME2-ME4).  out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); accumulation order is fixed
  * (offset index ascending, then input channel), so results are bit-reproducible run to run. */
-int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, int K, long n_out,
+int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, long nbr_pitch, int K, long n_out,
                      const float *weight, const float *bias, int cout, int act, float *out, void *stream);
 
-/* bf16 tensor-core path (tcgen05, fp32 accumulation in TMEM).  cin % 8 == 0 (zero-padded to 64-wide
- * K chunks), cout % 16 == 0, 16 <= cout <= 256, K <= 128.  feats_bf16: N_in x cin bf16 rows;
- * wpacked from pcg_pack_weights_bf16; out_f32 and/or out_bf16 may be NULL. */
+/* bf16 tensor-core path (tcgen05.mma, fp32 accumulation in TMEM, operands gathered by TMA tile::gather4).
+ * 1 <= cout <= 256, K <= 128, any cin >= 1, n_in >= 1.  feats_bf16: n_in rows of pcg_tc_cin_padded(cin) bf16
+ * (16, 32 or a multiple of 64 channels, zero padded; pcg_f32_to_bf16_rows makes them); wpacked from
+ * pcg_pack_weights_bf16.  cout is padded to the 16-column MMA granule internally, so the occupancy / colour
+ * heads and the 4-channel input layer run on the same kernel.  out_f32 and/or out_bf16 (cout % 16 == 0 only)
+ * may be NULL. */
+int pcg_tc_cin_padded(int cin);
 size_t pcg_packed_weight_bytes(int K, int cin, int cout);
 int pcg_pack_weights_bf16(const float *weight, int K, int cin, int cout, void *wpacked, void *stream);
-int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, const uint32_t *tile_mask,
-                    int K, long n_out, const void *wpacked, const float *bias, int cout, int act,
-                    float *out_f32, void *out_bf16, void *stream);
+int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                    const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                    int act, float *out_f32, void *out_bf16, void *stream);
 int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
+/* n rows of c floats -> n rows of c_padded >= c bf16, zero padded. */
+int pcg_f32_to_bf16_rows(const float *src, long n, int c, int c_padded, void *dst, void *stream);
 
 /* Channel-wise convolution out[o][c] = sum_i F[nbr[i][o]][c] * w[i][c or 0]
  * (ME.MinkowskiChannelwiseConvolution, loss.py:185-188; w_cols = C or 1). */
-int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, int K, long n_out, const float *w,
-                         int w_cols, float *out, void *stream);
+int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, long nbr_pitch, int K, long n_out,
+                         const float *w, int w_cols, float *out, void *stream);
 
 /* Elementwise activation on features (ME.MinkowskiReLU / MinkowskiLeakyReLU, ME7). */
 int pcg_activation(const float *x, long n, int act, float *out, void *stream);

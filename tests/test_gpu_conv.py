@@ -64,7 +64,8 @@ def test_tc_path_is_exact_on_bf16_representable_inputs(pkg, dev):
     so = pkg.sparse_ops
     C, cs = setup(dev, pkg, seed=11)
     rng = np.random.default_rng(0)
-    for cin, cout, ksize in ((64, 32, 3), (128, 128, 3), (192, 256, 3), (32, 16, 3)):
+    for cin, cout, ksize in ((64, 32, 3), (128, 128, 3), (192, 256, 3), (32, 16, 3), (16, 1, 3), (8, 24, 3), (4, 32, 5),
+                            (40, 48, 3), (64, 1, 3), (3, 5, 3)):
         Fm = rng.integers(-4, 5, (len(C), cin)).astype(np.float32)
         W = rng.integers(-2, 3, (ksize ** 3, cin, cout)).astype(np.float32)
         b = rng.integers(-3, 4, (1, cout)).astype(np.float32)
@@ -126,3 +127,41 @@ def test_channelwise_conv_k9(pkg, dev):
     ref = mod(me_ref.SparseTensor(Fm, torch.from_numpy(C))).F.detach()
     out = so.channelwise_conv(Fm.to(dev), cs, w.to(dev), 9).cpu()
     assert rel_l2(out.numpy(), ref.numpy()) < 1e-5
+
+
+def test_topk_selection_consistent_with_fp32_logits(pkg, dev):
+    """Occupancy head (conv k3 + ReLU + conv k3 -> 1 logit) on bf16 tensor cores, then top-k (transforms.py:146-160,
+    228-254): the logits match the fp32 oracle to 1e-2 relative L2, and every selection difference lies inside the
+    numerical error band around the oracle's k-th logit -- reduced precision can only flip near-ties."""
+    so = pkg.sparse_ops
+    C, cs = setup(dev, pkg, seed=21, ts=2)
+    cand = cs.generated(5, 2)
+    Cc = cand.coords.cpu().numpy()
+    n = len(Cc)
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((n, 32)).astype(np.float32)
+    W1 = (rng.standard_normal((27, 32, 16)) / np.sqrt(32 * 27) * 2).astype(np.float32)
+    b1 = (rng.standard_normal((1, 16)) * 0.1).astype(np.float32)
+    W2 = (rng.standard_normal((27, 16, 1)) / np.sqrt(16 * 27) * 2).astype(np.float32)
+    b2 = np.zeros((1, 1), np.float32)
+    nbr = native.kernel_map(Cc, Cc, 3, 1, False)
+    ref = native.conv(native.conv(X, nbr, W1, b1, 1), nbr, W2, b2, 0)[:, 0]
+    t = lambda a: torch.from_numpy(a).to(dev)
+    prev = so.set_conv_mode("tc")
+    try:
+        h = so.sparse_conv(t(X), cand, cand, t(W1), t(b1), 3, False, act=so.ACT_RELU, out="bf16")
+        assert h.dtype == torch.bfloat16
+        logits = so.sparse_conv(h, cand, cand, t(W2), t(b2), 3, False)[:, 0]
+    finally:
+        so.set_conv_mode(prev)
+    mine = logits.cpu().numpy()
+    assert rel_l2(mine, ref) < 1e-2
+    k = n // 5
+    mask = so.topk_mask(logits, cand.coords, [k]).cpu().numpy()
+    assert mask.sum() == k
+    thr = np.sort(ref)[-k]
+    band = 2.0 * np.abs(mine - ref).max()
+    assert (ref[mask] >= thr - band).all() and (ref[~mask] <= thr + band).all()
+    exact = np.zeros(n, bool)
+    exact[np.argsort(-ref, kind="stable")[:k]] = True
+    print(f"top-k agreement with the fp32 selection: {(mask & exact).sum() / k:.4f} (error band {band:.2e}, logit std {ref.std():.2e})")

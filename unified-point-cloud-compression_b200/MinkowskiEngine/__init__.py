@@ -126,6 +126,7 @@ class MinkowskiConvolutionBase(nn.Module):
         self.bias = nn.Parameter(torch.empty(1, self.out_channels)) if bias else None
         self._packed = so.PackedWeights()
         self.fused_activation = so.ACT_NONE      # host mirror may fuse the following (Leaky)ReLU into the epilogue
+        self.emit = "f32"                        # "both": also write the bf16 shadow the next tensor-core layer reads
         self.reset_parameters()
 
     def reset_parameters(self, is_transpose=None):
@@ -164,7 +165,7 @@ class MinkowskiConvolutionBase(nn.Module):
                                        self.is_transpose, self.fused_activation)
         else:
             out = so.sparse_conv(input.F, in_set, out_set, self.kernel, self.bias, self.kernel_size, self.is_transpose,
-                                 act=self.fused_activation, packed=self._packed)
+                                 act=self.fused_activation, packed=self._packed, out=self.emit)
         return SparseTensor(out, _coord_set=out_set)
 
 

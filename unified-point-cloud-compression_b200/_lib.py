@@ -20,21 +20,24 @@ _PROTOS = {
     "pcg_version": (_I, []),
     "pcg_launch_count": (_L, []),
     "pcg_hash_capacity": (_L, [_L]),
+    "pcg_nbr_pitch": (_L, [_L]),
+    "pcg_tc_cin_padded": (_I, [_I]),
     "pcg_scratch_bytes": (_SZ, [_L]),
     "pcg_hash_build": (_I, [_P, _L, _P, _P, _L, _P]),
     "pcg_hash_lookup": (_I, [_P, _P, _L, _P, _L, _P, _P]),
     "pcg_unique_first": (_I, [_P, _L, _P, _P, _L, _P, _P, _P, _P, _SZ, _P]),
     "pcg_stride_coords": (_I, [_P, _L, _I, _P, _P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_generate_coords": (_I, [_P, _L, _I, _I, _I, _P, _P, _L, _P, _L, _P, _P, _P, _SZ, _P]),
-    "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _P, _P]),
+    "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _L, _P, _P]),
     "pcg_sort_rows": (_I, [_P, _L, _I, _P, _P, _SZ, _P]),
     "pcg_sort_rows_scratch_bytes": (_SZ, [_L]),
-    "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _I, _L, _P, _P, _I, _I, _P, _P]),
+    "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P]),
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),
     "pcg_pack_weights_bf16": (_I, [_P, _I, _I, _I, _P, _P]),
-    "pcg_conv_fwd_tc": (_I, [_P, _L, _I, _P, _P, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
+    "pcg_conv_fwd_tc": (_I, [_P, _L, _I, _P, _L, _P, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
     "pcg_f32_to_bf16": (_I, [_P, _P, _L, _P]),
-    "pcg_channelwise_conv": (_I, [_P, _I, _P, _I, _L, _P, _I, _P, _P]),
+    "pcg_f32_to_bf16_rows": (_I, [_P, _L, _I, _I, _P, _P]),
+    "pcg_channelwise_conv": (_I, [_P, _I, _P, _L, _I, _L, _P, _I, _P, _P]),
     "pcg_activation": (_I, [_P, _L, _I, _P, _P]),
     "pcg_gdn_fwd": (_I, [_P, _L, _I, _P, _P, _I, _P, _P]),
     "pcg_topk_mask": (_I, [_P, _P, _L, _I, _L, _P, _P, _SZ, _P]),

@@ -13,7 +13,7 @@
 #define KC 16
 
 __global__ void __launch_bounds__(256) k_conv_tile_f32(const float *__restrict__ feats, int cin,
-                                                       const int32_t *__restrict__ nbr, int K, long n_out,
+                                                       const int32_t *__restrict__ nbr, long pitch, int K, long n_out,
                                                        const float *__restrict__ weight, const float *__restrict__ bias,
                                                        int cout, int act, float *__restrict__ out) {
     __shared__ __align__(16) float As[KC][TM + 4];
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256) k_conv_tile_f32(const float *__restrict__
         const int a_row = t >> 2, a_quad = t & 3;
         const long o = row0 + a_row;
         for (int k = 0; k < K; ++k) {
-            int nb = (o < n_out) ? __ldg(nbr + (long)k * n_out + o) : -1;
+            int nb = (o < n_out) ? __ldg(nbr + (long)k * pitch + o) : -1;
             if (!__syncthreads_or(nb >= 0)) continue;  // no row of this tile has offset k
             const float *src = nb >= 0 ? feats + (long)nb * cin : nullptr;
             for (int c0 = 0; c0 < cin; c0 += KC) {
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) k_conv_tile_f32(const float *__restrict__
                 float v = 0.f;
                 if (j < flat_total && o < n_out) {
                     int k = (int)(j / cin), c = (int)(j - (long)k * cin);
-                    int nb = __ldg(nbr + (long)k * n_out + o);
+                    int nb = __ldg(nbr + (long)k * pitch + o);
                     if (nb >= 0) { v = __ldg(feats + (long)nb * cin + c); any = 1; }
                 }
                 As[jj][r] = v;
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(256) k_conv_tile_f32(const float *__restrict__
 // cin/LPR channels (float4 gathers), fixed-order xor-shuffle reduction.
 template <int LPR>
 __global__ void __launch_bounds__(256) k_conv_narrow_f32(const float *__restrict__ feats, int cin,
-                                                         const int32_t *__restrict__ nbr, int K, long n_out,
+                                                         const int32_t *__restrict__ nbr, long pitch, int K, long n_out,
                                                          const float *__restrict__ weight, const float *__restrict__ bias,
                                                          int cout, int act, float *__restrict__ out) {
     extern __shared__ __align__(16) float wsm[];  // [K][cin][4] (cout padded to 4)
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(256) k_conv_narrow_f32(const float *__restrict
         const bool live = o < n_out;
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
         for (int k = 0; k < K; ++k) {
-            int nb = live ? __ldg(nbr + (long)k * n_out + o) : -1;
+            int nb = live ? __ldg(nbr + (long)k * pitch + o) : -1;
             if (nb < 0) continue;
             const float4 *src = reinterpret_cast<const float4 *>(feats + (long)nb * cin);
             for (int v = sub; v < vec_per_row; v += LPR) {
@@ -181,38 +181,38 @@ __global__ void __launch_bounds__(256) k_conv_narrow_f32(const float *__restrict
 }
 
 template <int LPR>
-static int launch_narrow(const float *feats, int cin, const int32_t *nbr, int K, long n_out, const float *weight,
+static int launch_narrow(const float *feats, int cin, const int32_t *nbr, long pitch, int K, long n_out, const float *weight,
                          const float *bias, int cout, int act, float *out, cudaStream_t st) {
     size_t smem = (size_t)K * cin * 4 * sizeof(float);
     PCG_CUDA(cudaFuncSetAttribute(k_conv_narrow_f32<LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long rows_per_block = 256 / LPR;
     long blocks = cdiv(n_out, rows_per_block);
     if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
-    k_conv_narrow_f32<LPR><<<(unsigned)blocks, 256, smem, st>>>(feats, cin, nbr, K, n_out, weight, bias, cout, act, out);
+    k_conv_narrow_f32<LPR><<<(unsigned)blocks, 256, smem, st>>>(feats, cin, nbr, pitch, K, n_out, weight, bias, cout, act, out);
     PCG_LAUNCHED();
     return 0;
 }
 
-extern "C" int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, int K, long n_out,
+extern "C" int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, long pitch, int K, long n_out,
                                 const float *weight, const float *bias, int cout, int act, float *out, void *stream) {
     (void)n_in;
     PCG_CHECK_ARG(cin >= 1 && cout >= 1 && K >= 1, "pcg_conv_fwd_f32: cin=%d cout=%d K=%d", cin, cout, K);
     if (n_out <= 0) return 0;
     cudaStream_t st = as_stream(stream);
     if (cout <= 4 && (cin & 3) == 0 && (size_t)K * cin * 16 <= 200 * 1024) {
-        if (cin >= 32) return launch_narrow<8>(feats, cin, nbr, K, n_out, weight, bias, cout, act, out, st);
-        if (cin >= 16) return launch_narrow<4>(feats, cin, nbr, K, n_out, weight, bias, cout, act, out, st);
-        return launch_narrow<1>(feats, cin, nbr, K, n_out, weight, bias, cout, act, out, st);
+        if (cin >= 32) return launch_narrow<8>(feats, cin, nbr, pitch, K, n_out, weight, bias, cout, act, out, st);
+        if (cin >= 16) return launch_narrow<4>(feats, cin, nbr, pitch, K, n_out, weight, bias, cout, act, out, st);
+        return launch_narrow<1>(feats, cin, nbr, pitch, K, n_out, weight, bias, cout, act, out, st);
     }
     dim3 grid((unsigned)cdiv(n_out, TM), (unsigned)cdiv(cout, TN));
-    k_conv_tile_f32<<<grid, 256, 0, st>>>(feats, cin, nbr, K, n_out, weight, bias, cout, act, out);
+    k_conv_tile_f32<<<grid, 256, 0, st>>>(feats, cin, nbr, pitch, K, n_out, weight, bias, cout, act, out);
     PCG_LAUNCHED();
     return 0;
 }
 
 // ---------------------------------------------------------------------------- channel-wise conv
 // out[o][c] = sum_k F[nbr[k][o]][c] * w[k][c or 0]   (ME.MinkowskiChannelwiseConvolution)
-__global__ void k_channelwise(const float *__restrict__ feats, int c, const int32_t *__restrict__ nbr, int K, long n_out,
+__global__ void k_channelwise(const float *__restrict__ feats, int c, const int32_t *__restrict__ nbr, long pitch, int K, long n_out,
                               const float *__restrict__ w, int w_cols, float *__restrict__ out) {
     long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
     long o = idx / c;
@@ -220,17 +220,17 @@ __global__ void k_channelwise(const float *__restrict__ feats, int c, const int3
     if (o >= n_out) return;
     float acc = 0.f;
     for (int k = 0; k < K; ++k) {
-        int nb = __ldg(nbr + (long)k * n_out + o);
+        int nb = __ldg(nbr + (long)k * pitch + o);
         if (nb >= 0) acc = fmaf(__ldg(feats + (long)nb * c + ch), __ldg(w + (long)k * w_cols + (w_cols == 1 ? 0 : ch)), acc);
     }
     out[idx] = acc;
 }
 
-extern "C" int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, int K, long n_out, const float *w,
-                                    int w_cols, float *out, void *stream) {
+extern "C" int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, long pitch, int K, long n_out,
+                                    const float *w, int w_cols, float *out, void *stream) {
     PCG_CHECK_ARG(w_cols == 1 || w_cols == c, "pcg_channelwise_conv: w_cols=%d must be 1 or C=%d", w_cols, c);
     if (n_out <= 0) return 0;
-    k_channelwise<<<(unsigned)cdiv(n_out * c, 256), 256, 0, as_stream(stream)>>>(feats, c, nbr, K, n_out, w, w_cols, out);
+    k_channelwise<<<(unsigned)cdiv(n_out * c, 256), 256, 0, as_stream(stream)>>>(feats, c, nbr, pitch, K, n_out, w, w_cols, out);
     PCG_LAUNCHED();
     return 0;
 }

@@ -3,17 +3,21 @@
 //
 //   out[o][:] = act(bias + sum_{k active} F[nbr[k][o]][:] @ W[k])       (bf16 x bf16 -> fp32)
 //
-// One CTA owns one 128-row output tile (UMMA M = 128, N = cout <= 256, K = 16 per instruction):
-//   warps 0-3  producers, then epilogue.  Thread r gathers input row nbr[k][r] of every active
-//              kernel offset k straight into the K-major SWIZZLE_128B operand image with
-//              16-byte cp.async (zero-fill for absent neighbours); thread 0 also starts the
-//              bulk (TMA 1-D) copy of the pre-swizzled weight slice.  Completion is published
-//              to the MMA warp through mbarriers after fence.proxy.async.
-//   warp 4     allocates TMEM, one elected lane issues tcgen05.mma and commits each stage back
-//              to the producers (tcgen05.commit -> mbarrier).
-// Kernel offsets no row of the tile uses are skipped (tile_mask from pcg_kernel_map).  Every output
-// element is one fixed-order chain of MMAs over ascending (k, cin-chunk): bit-reproducible, and
-// independent of which tile a row lands in (absent neighbours contribute exact zeros).
+// One CTA owns one 128-row output tile (UMMA M = 128, N = roundup16(cout) <= 256, K = 16 per instruction):
+//   warps 0-3  producers, then epilogue.  The gather is done by the TMA unit: lane l of a producer warp loads the
+//              four neighbour indices nbr[k][4l..4l+3] of a kernel offset as one int4 and issues ONE
+//              cp.async.bulk.tensor tile::gather4, which fetches those four feature rows straight into the
+//              K-major swizzled operand image (absent neighbours are index -1 = out of bounds = zero fill).
+//              A warp-wide issue therefore fills a whole 128-row operand sub-tile; the matching pre-swizzled
+//              weight slice arrives through a 1-D bulk copy.  Both complete on the stage's mbarrier (expect_tx).
+//   warp 4     allocates TMEM, one elected lane issues tcgen05.mma and commits each stage back to the producers.
+// Operand rows are RB = 32 / 64 / 128 bytes (cin = 16 / 32 / >= 33 after padding) with the matching 32B / 64B / 128B
+// swizzle, so narrow layers (occupancy heads, input layer) move no padding; a 16 KiB stage holds 128/RB kernel
+// offsets.  Kernel offsets no row of the tile uses are skipped (tile_mask from pcg_kernel_map).  Every output element
+// is one fixed-order chain of MMAs over ascending (k, cin-chunk): bit-reproducible, and independent of which
+// tile a row lands in (absent neighbours contribute exact zeros).
+#include <cuda.h>
+
 #include "pcg_common.cuh"
 
 #define TC_ROWS 128
@@ -90,30 +94,53 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// K-major swizzled shared-memory matrix descriptor for rows of RB bytes (8-row groups 8*RB bytes apart)
+template <int RB>
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    constexpr uint64_t layout = RB == 128 ? 2 : (RB == 64 ? 4 : 6);   // SWIZZLE_128B / 64B / 32B
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);  // start address
+    d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)((8 * RB) >> 4) << 32;     // stride byte offset between 8-row groups
+    d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
+    d |= layout << 61;
+    return d;
+}
+
+// four feature rows (row indices r.x..r.w, column `col`) -> four consecutive operand rows at `dst`
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap *tm, int col, int4 r, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+        ::"r"(dst), "l"(tm), "r"(col), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(bar)
+        : "memory");
+}
+
 struct TcParams {
-    const __nv_bfloat16 *feats;
-    const int32_t *nbr;
-    const uint32_t *tile_mask;
-    const uint8_t *wpacked;
+    const int32_t *nbr;           // [K][nbr_pitch], padding entries -1
+    const uint32_t *tile_mask;    // [tiles][4]
+    const uint8_t *wpacked;       // [k][chunk][cout_p][RB bytes] pre-swizzled
     const float *bias;
     float *out_f32;
     __nv_bfloat16 *out_bf16;
-    long n_out;
-    int cin, cout, K;
-    int chunks;      // ceil(cin / 64)
+    long n_out, nbr_pitch;
+    int cout, cout_p, K;
+    int chunks;      // RB == 128: 64-wide K chunks per kernel offset; otherwise 1
     int stages;
-    int tmem_cols;   // power of two >= max(32, cout)
+    int tmem_cols;   // power of two >= max(32, cout_p)
     int act;
 };
 
-__global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
+template <int RB>
+__global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtensorMap tm, const TcParams p) {
+    constexpr int G = 128 / RB;                  // operand sub-tiles (kernel offsets) per 16 KiB stage
+    constexpr uint32_t SUB_A = TC_ROWS * RB;     // bytes of one A sub-tile
     extern __shared__ uint8_t smem_raw[];
-    // 1024-byte aligned operand ring (SWIZZLE_128B requirement), barriers behind it
+    // 1024-byte aligned operand ring (swizzle atom alignment), barriers behind it
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     uint8_t *sm = smem_raw + (base - raw);
-    const uint32_t b_bytes = (uint32_t)p.cout * 128u;
-    const uint32_t stage_bytes = TC_A_BYTES + b_bytes;
+    const uint32_t sub_b = (uint32_t)p.cout_p * RB;            // bytes of one B sub-tile
+    const uint32_t stage_bytes = TC_A_BYTES + G * sub_b;
     uint8_t *ctl = sm + (size_t)p.stages * stage_bytes;
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(ctl);            // [stages]
     uint64_t *empty_bar = full_bar + TC_MAX_STAGES;                    // [stages]
@@ -127,7 +154,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            mbar_init(smem_u32(full_bar + s), TC_ROWS);   // 128 producer arrivals (+ weight bytes via tx)
+            mbar_init(smem_u32(full_bar + s), 1);         // one arrive.expect_tx; data arrives as tx bytes
             mbar_init(smem_u32(empty_bar + s), 1);        // one tcgen05.commit
         }
         mbar_init(smem_u32(accum_bar), 1);
@@ -159,51 +186,55 @@ __global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
     tc_fence_after();
     const uint32_t tmem_d = *tmem_slot;
     const int n_active = *n_active_s;
-    const int n_items = n_active * p.chunks;
+    const int n_sub = n_active * p.chunks;              // operand sub-tiles of this tile
+    const int n_items = (n_sub + G - 1) / G;            // pipeline stages to run
 
     if (warp < 4) {
-        // ------------------------------------------------------------------ producers
-        const int r = tid;
-        const long o = tile * TC_ROWS + r;
-        const bool live = o < p.n_out;
-        const uint32_t row_off = (uint32_t)r * 128u;
-        const uint32_t xr = (uint32_t)(r & 7);
-        int nb = -1;
-        for (int it = 0; it < n_items; ++it) {
-            const int s = it % p.stages;
-            const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-            const int a = it / p.chunks, cc = it - a * p.chunks;
-            const int k = active[a];
-            if (cc == 0) nb = live ? __ldg(p.nbr + (long)k * p.n_out + o) : -1;
-            mbar_wait(smem_u32(empty_bar + s), ph ^ 1u);
-            const uint32_t a_dst = base + (uint32_t)s * stage_bytes + row_off;
-            const int c0 = cc * TC_KCHUNK;
-            const __nv_bfloat16 *src = p.feats + (nb >= 0 ? (long)nb * p.cin + c0 : 0);
+        // ------------------------------------------------------------------ producers (item it -> warp it % P)
+        // P <= stages: a warp is then never two ring wraps ahead of the consumer, which the 1-bit mbarrier
+        // phase parity could not tell apart from "slot free".
+        const int P = p.stages < 4 ? p.stages : 4;
+        const int32_t *nbr_tile = p.nbr + tile * TC_ROWS + lane * 4;
+        int s = warp, wrap = 0;                            // stage slot / how often the ring wrapped, for item `it`
+        while (s >= p.stages) { s -= p.stages; ++wrap; }
+        int a = 0, cc = 0;                                 // RB == 128: (active offset, chunk) of item `it`
+        if (RB == 128) { cc = warp; while (cc >= p.chunks) { cc -= p.chunks; ++a; } }
+        int4 idx[G];
+        auto load_idx = [&](int it_, int a_) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const bool ok = nb >= 0 && (c0 + j * 8) < p.cin;
-                cp_async16(a_dst + (((uint32_t)j ^ xr) << 4), ok ? (const void *)(src + j * 8) : (const void *)p.feats, ok ? 16u : 0u);
+            for (int g = 0; g < G; ++g) {
+                const int aa = RB == 128 ? a_ : it_ * G + g;
+                idx[g] = aa < n_active ? __ldg(reinterpret_cast<const int4 *>(nbr_tile + (long)active[aa] * p.nbr_pitch))
+                                       : make_int4(-1, -1, -1, -1);
             }
-            cp_async_commit();
-            if (tid == 0) {
-                const uint32_t fb = smem_u32(full_bar + s);
-                mbar_expect_tx(fb, b_bytes);
-                bulk_g2s(base + (uint32_t)s * stage_bytes + TC_A_BYTES,
-                         p.wpacked + ((size_t)k * p.chunks + cc) * b_bytes, b_bytes, fb);
+        };
+        if (warp < P && warp < n_items) load_idx(warp, a);
+        for (int it = warp; warp < P && it < n_items; it += P) {
+            const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;     // sub-tiles in this item
+            const uint32_t fb = smem_u32(full_bar + s);
+            const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+            mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"((uint32_t)subs * (SUB_A + sub_b)) : "memory");
             }
-            if (it >= TC_LAG) {
-                cp_async_wait<TC_LAG>();
-                fence_proxy_async();
-                mbar_arrive(smem_u32(full_bar + (it - TC_LAG) % p.stages));
+            __syncwarp();
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+                if (g < subs) tma_gather4(a_base + g * SUB_A + (uint32_t)lane * 4u * RB, &tm, cc * TC_KCHUNK, idx[g], fb);
+            if (lane < subs) {
+                const int k = RB == 128 ? active[a] : active[it * G + lane];
+                bulk_g2s(a_base + TC_A_BYTES + lane * sub_b, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
             }
+            // advance this warp's cursor by P items and prefetch the next item's neighbour indices
+            s += P;
+            while (s >= p.stages) { s -= p.stages; ++wrap; }
+            if (RB == 128) { cc += P; while (cc >= p.chunks) { cc -= p.chunks; ++a; } }
+            if (it + P < n_items) load_idx(it + P, a);
         }
-        // drain the last TC_LAG groups
-        cp_async_wait<0>();
-        fence_proxy_async();
-        for (int it = (n_items > TC_LAG ? n_items - TC_LAG : 0); it < n_items; ++it)
-            mbar_arrive(smem_u32(full_bar + it % p.stages));
 
         // ------------------------------------------------------------------ epilogue
+        const long o = tile * TC_ROWS + tid;
+        const bool live = o < p.n_out;
         if (n_items > 0) {
             mbar_wait(smem_u32(accum_bar), 0);
             tc_fence_after();
@@ -220,22 +251,28 @@ __global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
                 float f[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + c0 + j) : 0.f), p.act);
-                if (p.out_f32) {
-                    float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
+                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
+                if ((p.cout & 15) == 0) {
+                    if (p.out_f32) {
+                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-                }
-                if (p.out_bf16) {
-                    uint32_t pk[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
-                        pk[j] = *reinterpret_cast<uint32_t *>(&h);
+                        for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
                     }
-                    uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
-                    dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    if (p.out_bf16) {
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                            pk[j] = *reinterpret_cast<uint32_t *>(&h);
+                        }
+                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
+                        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
+                } else if (p.out_f32) {   // narrow heads (cout = 1, 3, ...): scalar stores of the real columns
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
                 }
             }
         }
@@ -243,18 +280,25 @@ __global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
     } else {
         // ------------------------------------------------------------------ MMA issuer
         if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.cout >> 3) << 17) | ((TC_ROWS >> 4) << 24);
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.cout_p >> 3) << 17) | ((TC_ROWS >> 4) << 24);
+            int s = 0;
+            uint32_t ph = 0;
             for (int it = 0; it < n_items; ++it) {
-                const int s = it % p.stages;
-                const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+                const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;
                 mbar_wait(smem_u32(full_bar + s), ph);
                 tc_fence_after();
                 const uint32_t a_addr = base + (uint32_t)s * stage_bytes;
-                const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(a_addr + TC_A_BYTES);
 #pragma unroll
-                for (int kk = 0; kk < TC_KCHUNK / 16; ++kk)  // +32 B per K=16 step inside the swizzle atom
-                    umma_bf16(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (it | kk) ? 1u : 0u);
+                for (int g = 0; g < G; ++g) {
+                    if (g < subs) {
+                        const uint64_t adesc = umma_desc<RB>(a_addr + g * SUB_A), bdesc = umma_desc<RB>(a_addr + TC_A_BYTES + g * sub_b);
+#pragma unroll
+                        for (int kk = 0; kk < RB / 32; ++kk)  // +32 B per K=16 step inside the swizzle atom
+                            umma_bf16(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (it | g | kk) ? 1u : 0u);
+                    }
+                }
                 umma_commit(smem_u32(empty_bar + s));
+                if (++s == p.stages) { s = 0; ph ^= 1u; }
             }
             if (n_items > 0) umma_commit(smem_u32(accum_bar));
         }
@@ -268,72 +312,122 @@ __global__ void __launch_bounds__(160) k_conv_tc(const TcParams p) {
 }
 
 // ---------------------------------------------------------------------------- weight packing
-// wpacked[(k*chunks + cc)][n][64] bf16: B operand image (N rows x 64 K-elements, K-major, 128B swizzle)
-// element (n, kk) <- W[k][cc*64 + kk][n] (zero beyond cin)
-__global__ void k_pack_weights(const float *__restrict__ w, int K, int cin, int cout, int chunks, __nv_bfloat16 *__restrict__ out) {
-    long total = (long)K * chunks * cout * 64;
+static inline int tc_cin_p(int cin) { return cin <= 16 ? 16 : (cin <= 32 ? 32 : ((cin + 63) & ~63)); }   // operand row width
+static inline int tc_cout_p(int cout) { return (cout + 15) & ~15; }
+static inline int tc_rb(int cin_p) { return cin_p == 16 ? 32 : (cin_p == 32 ? 64 : 128); }
+
+// wpacked[(k*chunks + cc)][n][RB/2] bf16 = B operand sub-tile (N rows of RB bytes, K-major, RB-byte swizzle):
+// element (n, kk) <- W[k][cc*64 + kk][n] (zero beyond cin / cout), its 16-byte chunk XOR-swizzled with the row.
+__global__ void k_pack_weights(const float *__restrict__ w, int K, int cin, int cout, int cout_p, int chunks, int rb,
+                               __nv_bfloat16 *__restrict__ out) {
+    const int kw = rb / 2;                       // K elements per operand row
+    long total = (long)K * chunks * cout_p * kw;
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     long stride = (long)gridDim.x * blockDim.x;
     for (; i < total; i += stride) {
-        int kk = (int)(i & 63);
-        long t = i >> 6;
-        int n = (int)(t % cout);
-        t /= cout;
+        int kk = (int)(i % kw);
+        long t = i / kw;
+        int n = (int)(t % cout_p);
+        t /= cout_p;
         int cc = (int)(t % chunks);
         int k = (int)(t / chunks);
         int c = cc * 64 + kk;
-        float v = c < cin ? __ldg(w + ((long)k * cin + c) * cout + n) : 0.f;
-        long stage = ((long)k * chunks + cc) * cout * 64;  // elements
-        int chunk16 = (kk >> 3) ^ (n & 7);
-        out[stage + (long)n * 64 + chunk16 * 8 + (kk & 7)] = __float2bfloat16_rn(v);
+        float v = (c < cin && n < cout) ? __ldg(w + ((long)k * cin + c) * cout + n) : 0.f;
+        long sub = ((long)k * chunks + cc) * cout_p * kw;  // elements
+        int xr = rb == 128 ? (n & 7) : (rb == 64 ? ((n >> 1) & 3) : ((n >> 2) & 1));
+        int chunk16 = (kk >> 3) ^ xr;
+        out[sub + (long)n * kw + chunk16 * 8 + (kk & 7)] = __float2bfloat16_rn(v);
     }
 }
 
 extern "C" size_t pcg_packed_weight_bytes(int K, int cin, int cout) {
-    int chunks = (cin + 63) / 64;
-    return (size_t)K * chunks * cout * 128;
+    const int cin_p = tc_cin_p(cin), cout_p = tc_cout_p(cout), rb = tc_rb(cin_p);
+    const int chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
+    return (size_t)K * chunks * cout_p * rb;
 }
 
 extern "C" int pcg_pack_weights_bf16(const float *weight, int K, int cin, int cout, void *wpacked, void *stream) {
     PCG_CHECK_ARG(K >= 1 && cin >= 1 && cout >= 1, "pcg_pack_weights_bf16: K=%d cin=%d cout=%d", K, cin, cout);
-    int chunks = (cin + 63) / 64;
-    long total = (long)K * chunks * cout * 64;
+    const int cin_p = tc_cin_p(cin), cout_p = tc_cout_p(cout), rb = tc_rb(cin_p);
+    const int chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
+    long total = (long)K * chunks * cout_p * (rb / 2);
     long blocks = cdiv(total, 256);
     if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
-    k_pack_weights<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(weight, K, cin, cout, chunks,
+    k_pack_weights<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(weight, K, cin, cout, cout_p, chunks, rb,
                                                                    reinterpret_cast<__nv_bfloat16 *>(wpacked));
     PCG_LAUNCHED();
     return 0;
 }
 
-extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, const uint32_t *tile_mask,
-                               int K, long n_out, const void *wpacked, const float *bias, int cout, int act,
-                               float *out_f32, void *out_bf16, void *stream) {
-    (void)n_in;
-    PCG_CHECK_ARG(cin % 8 == 0 && cin >= 8, "pcg_conv_fwd_tc: cin=%d must be a multiple of 8", cin);
-    PCG_CHECK_ARG(cout % 16 == 0 && cout >= 16 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be a multiple of 16 in [16,256]", cout);
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*PcgEncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PcgEncodeTiled tensor_map_encoder() {
+    static PcgEncodeTiled fn = []() -> PcgEncodeTiled {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess) return nullptr;
+        return reinterpret_cast<PcgEncodeTiled>(p);
+    }();
+    return fn;
+}
+
+extern "C" int pcg_tc_cin_padded(int cin) { return tc_cin_p(cin); }
+
+template <int RB>
+static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cudaStream_t st) {
+    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_conv_tc<RB><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                               int act, float *out_f32, void *out_bf16, void *stream) {
+    PCG_CHECK_ARG(cin >= 1 && cin <= 1024, "pcg_conv_fwd_tc: cin=%d", cin);
+    PCG_CHECK_ARG(cout >= 1 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be in [1,256]", cout);
+    PCG_CHECK_ARG(out_bf16 == nullptr || (cout & 15) == 0, "pcg_conv_fwd_tc: a bf16 output needs cout %% 16 == 0 (cout=%d)", cout);
     PCG_CHECK_ARG(K >= 1 && K <= 128, "pcg_conv_fwd_tc: K=%d must be <= 128", K);
     PCG_CHECK_ARG(tile_mask != nullptr, "pcg_conv_fwd_tc: tile_mask required");
+    PCG_CHECK_ARG(nbr_pitch >= n_out && (nbr_pitch & 127) == 0 && ((uintptr_t)nbr & 15) == 0,
+                  "pcg_conv_fwd_tc: nbr must be 16-byte aligned with a pitch that is a multiple of 128 (pitch=%ld)", nbr_pitch);
+    PCG_CHECK_ARG(n_in >= 1, "pcg_conv_fwd_tc: n_in=%ld (an empty input has no tensor map)", n_in);
     PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)wpacked & 15) == 0, "pcg_conv_fwd_tc: operands must be 16-byte aligned");
     if (n_out <= 0) return 0;
+    const int cin_p = tc_cin_p(cin), rb = tc_rb(cin_p);
+    PcgEncodeTiled encode = tensor_map_encoder();
+    PCG_CHECK_ARG(encode != nullptr, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled is not available from this driver");
+    CUtensorMap tm;
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)cin_p, (cuuint64_t)n_in};
+        cuuint64_t strides[1] = {(cuuint64_t)cin_p * 2};
+        cuuint32_t box[2] = {(cuuint32_t)(rb / 2), 1};                  // tile::gather4: one row per index
+        cuuint32_t estr[2] = {1, 1};
+        CUtensorMapSwizzle sw = rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+        CUresult r = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(feats_bf16), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        PCG_CHECK_ARG(r == CUDA_SUCCESS, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled failed (%d) for n_in=%ld cin_p=%d", (int)r, n_in, cin_p);
+    }
     TcParams p;
-    p.feats = reinterpret_cast<const __nv_bfloat16 *>(feats_bf16);
-    p.nbr = nbr; p.tile_mask = tile_mask;
+    p.nbr = nbr; p.nbr_pitch = nbr_pitch; p.tile_mask = tile_mask;
     p.wpacked = reinterpret_cast<const uint8_t *>(wpacked);
     p.bias = bias; p.out_f32 = out_f32; p.out_bf16 = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
-    p.n_out = n_out; p.cin = cin; p.cout = cout; p.K = K;
-    p.chunks = (cin + 63) / 64;
+    p.n_out = n_out; p.cout = cout; p.cout_p = tc_cout_p(cout); p.K = K;
+    p.chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
     p.act = act;
     p.tmem_cols = 32;
-    while (p.tmem_cols < cout) p.tmem_cols <<= 1;
-    const size_t stage_bytes = TC_A_BYTES + (size_t)cout * 128;
+    while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
+    const size_t stage_bytes = TC_A_BYTES + (size_t)p.cout_p * 128;
     int stages = (int)((108 * 1024) / stage_bytes);   // two CTAs per SM where the tile allows it
     if (stages < 3) stages = 3;
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
-    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_tc<<<(unsigned)cdiv(n_out, TC_ROWS), 160, smem, as_stream(stream)>>>(p);
-    PCG_LAUNCHED();
-    return 0;
+    cudaStream_t st = as_stream(stream);
+    if (rb == 32) return launch_tc<32>(tm, p, smem, st);
+    if (rb == 64) return launch_tc<64>(tm, p, smem, st);
+    return launch_tc<128>(tm, p, smem, st);
 }

@@ -89,6 +89,8 @@ extern "C" long pcg_hash_capacity(long n_keys) {
     return cap;
 }
 
+extern "C" long pcg_nbr_pitch(long n_out) { return n_out <= 0 ? 128 : (n_out + 127) / 128 * 128; }
+
 extern "C" size_t pcg_scratch_bytes(long n_items) { return pcg_compact_scratch_bytes(n_items) + 8192; }
 
 extern "C" int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, void *stream) {
@@ -335,7 +337,7 @@ extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int
 __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
                                                     uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
                                                     int ksize, int K, int step, int lattice, int32_t *__restrict__ nbr,
-                                                    uint32_t *__restrict__ tile_mask) {
+                                                    long pitch, uint32_t *__restrict__ tile_mask) {
     long o = (long)blockIdx.x * 128 + threadIdx.x;
     bool live = o < n_out;
     int4 c = live ? pcg_ld_coord(out_coords, o) : make_int4(0, 0, 0, 0);
@@ -354,8 +356,8 @@ __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__
                     // grid), so most offsets cannot hit for a given output parity -- no probe needed
                     bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
                     if (possible && pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
-                    nbr[(long)k * n_out + o] = row;
                 }
+                nbr[(long)k * pitch + o] = row;      // rows past n_out are the -1 padding of the last tile
                 if (tile_mask) {
                     unsigned any = __ballot_sync(0xffffffffu, row >= 0);
                     if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
@@ -368,16 +370,18 @@ __global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__
 }
 
 extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *out_coords, long n_out,
-                              int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, uint32_t *tile_mask,
-                              void *stream) {
+                              int ksize, int ts, int transposed, int in_lattice, int32_t *nbr, long nbr_pitch,
+                              uint32_t *tile_mask, void *stream) {
     PCG_CHECK_ARG(is_pow2(cap), "pcg_kernel_map: cap=%ld must be a power of two", cap);
     PCG_CHECK_ARG(ksize >= 1 && ksize <= 9 && ts >= 1, "pcg_kernel_map: ksize=%d ts=%d", ksize, ts);
     int K = ksize * ksize * ksize;
     PCG_CHECK_ARG(tile_mask == nullptr || K <= 128, "pcg_kernel_map: tile_mask needs ksize^3 <= 128 (got %d)", K);
+    PCG_CHECK_ARG(nbr_pitch == pcg_nbr_pitch(n_out), "pcg_kernel_map: nbr_pitch=%ld must be pcg_nbr_pitch(n_out)=%ld", nbr_pitch,
+                  pcg_nbr_pitch(n_out));
     if (n_out <= 0) return 0;
     int step = transposed ? -ts : ts;
     k_kernel_map<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
-                                                                           ksize, K, step, in_lattice, nbr, tile_mask);
+                                                                           ksize, K, step, in_lattice, nbr, nbr_pitch, tile_mask);
     PCG_LAUNCHED();
     return 0;
 }

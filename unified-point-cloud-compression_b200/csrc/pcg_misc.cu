@@ -44,6 +44,29 @@ extern "C" int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream
     return 0;
 }
 
+// rows of c floats -> rows of cp = roundup8(c) bf16 (zero padded): operand layout of pcg_conv_fwd_tc for odd widths
+__global__ void k_f32_to_bf16_rows(const float *__restrict__ src, long n, int c, int cp, __nv_bfloat16 *__restrict__ dst) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long total = n * cp;
+    long stride = (long)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        long r = i / cp;
+        int j = (int)(i - r * cp);
+        dst[i] = __float2bfloat16_rn(j < c ? __ldg(src + r * c + j) : 0.f);
+    }
+}
+
+extern "C" int pcg_f32_to_bf16_rows(const float *src, long n, int c, int cp, void *dst, void *stream) {
+    if (n <= 0) return 0;
+    PCG_CHECK_ARG(c >= 1 && cp >= c, "pcg_f32_to_bf16_rows: c=%d c_padded=%d", c, cp);
+    if (cp == c) return pcg_f32_to_bf16(src, dst, n * c, stream);
+    long blocks = cdiv(n * cp, 256);
+    if (blocks > PCG_SMS * 16) blocks = PCG_SMS * 16;
+    k_f32_to_bf16_rows<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(src, n, c, cp, reinterpret_cast<__nv_bfloat16 *>(dst));
+    PCG_LAUNCHED();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------- GDN1
 // norm[n][j] = beta[j] + sum_i gamma[j][i] * |x[n][i]|;  out = x * (1/norm)  or  x * norm.
 // 64x64 output tile per CTA, 16-deep smem stages, fixed ascending-i accumulation.

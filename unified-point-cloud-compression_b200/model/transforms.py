@@ -11,6 +11,8 @@ reference's checkpoints load.  Differences in *how* (not what):
   * `down_conv` is only ever used for its output coordinates (transforms.py:219-220, model.py:227-229):
     `coords_down()` derives them with the stride-coordinates kernel, no convolution.
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -72,6 +74,8 @@ class SparseSynthesisTransform(nn.Module):
         self.predict_3 = nn.Sequential(_conv(n1 // 4, n4 // 8, 3), ME.MinkowskiReLU(inplace=False), _conv(n4 // 8, 1, 3))
         self.prune = ME.MinkowskiPruning()
         self.down_conv = ME.MinkowskiConvolution(in_channels=1, out_channels=1, kernel_size=3, stride=2, dimension=3)
+        for up in (self.up_1, self.up_2, self.up_3):
+            up[-1].emit = "both"        # candidates feed the occupancy head (bf16 operand) and the prune (fp32 rows)
 
     # -- helpers -----------------------------------------------------------------------------
     @staticmethod
@@ -81,7 +85,7 @@ class SparseSynthesisTransform(nn.Module):
         if torch.is_grad_enabled() and x.F.requires_grad:
             return head(x)
         h = so.sparse_conv(x.F, x.coord_set, x.coord_set, first.kernel, first.bias, first.kernel_size, False,
-                           act=so.ACT_RELU, packed=first._packed)
+                           act=so.ACT_RELU, packed=first._packed, out="bf16")    # hidden rows only feed the next conv
         o = so.sparse_conv(h, x.coord_set, x.coord_set, last.kernel, last.bias, last.kernel_size, False,
                            packed=last._packed)
         return ME.SparseTensor(o, _coord_set=x.coord_set)
@@ -90,8 +94,14 @@ class SparseSynthesisTransform(nn.Module):
     def _topk_prediction(prediction, k):
         return so.topk_mask(prediction.F[:, 0], prediction.C, [int(v) for v in k])
 
-    def _prune_tensor(self, x, mask, n_keep=None):
+    def _prune_tensor(self, x, mask, n_keep=None, reorder=False):
+        """Rows under `mask`.  reorder=True additionally puts the survivors in Z-order (row order is free in ME
+        semantics): they are the parents of the next generative level, whose candidates inherit the parents'
+        order class by class -- without it spatial coherence (= L2 hit rate of every gather) decays level by level."""
         oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
+        if reorder and oc.shape[0] > 1 and not os.environ.get("PCG_NO_REORDER"):
+            perm = so.sort_rows(oc, morton=True)
+            oc, of = oc[perm].contiguous(), of[perm].contiguous()
         return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
 
     @staticmethod
@@ -113,7 +123,7 @@ class SparseSynthesisTransform(nn.Module):
             mask = self._topk_prediction(pred, k_level)
             n_avail = [x.F.shape[0]] if len(k_level) == 1 else count_per_batch(x)
             n_keep = sum(min(int(kk), na) for kk, na in zip(k_level, n_avail)) if len(n_avail) == len(k_level) else None
-            x = self._prune_tensor(x, mask, n_keep)
+            x = self._prune_tensor(x, mask, n_keep, reorder=head is not self.predict_3)
         x = self.color_conv(x)
         if coords is None:
             return x

@@ -143,7 +143,8 @@ class CoordSet:
 
     # -- kernel maps -------------------------------------------------------------------------
     def kernel_map(self, out_set, ksize, transposed):
-        """nbr[K][n_out] (rows of THIS set feeding each output row) + per-128-row-tile offset mask."""
+        """nbr[K][pitch] (rows of THIS set feeding each output row; pitch = n_out rounded up to 128, padding -1)
+        + per-128-row-tile offset mask."""
         key = (id(out_set), int(ksize), bool(transposed))
         hit = self._kmaps.get(key)
         if hit is None:
@@ -151,11 +152,12 @@ class CoordSet:
             dev = self.coords.device
             K = ksize ** 3
             ts = out_set.ts if transposed else self.ts
-            nbr = torch.empty((K, max(out_set.n, 1)), dtype=torch.int32, device=dev)
+            pitch = _lib.load().pcg_nbr_pitch(out_set.n)
+            nbr = torch.empty((K, pitch), dtype=torch.int32, device=dev)
             tiles = (out_set.n + 127) // 128
             tmask = torch.empty((max(tiles, 1), 4), dtype=torch.int32, device=dev) if K <= 128 else None
             call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
-                 int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), ptr(tmask), stream())
+                 int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), pitch, ptr(tmask), stream())
             hit = (nbr, tmask, None if out_set is self else out_set)   # keep out_set alive while cached (id() key)
             self._kmaps[key] = hit
         return hit[0], hit[1]
@@ -210,14 +212,24 @@ def lexsort(coords):
 
 
 # ----------------------------------------------------------------------------- features
+def cin_padded(c):
+    """Operand row width of the tensor-core path for c input channels (16, 32 or a multiple of 64)."""
+    return 16 if c <= 16 else (32 if c <= 32 else (c + 63) // 64 * 64)
+
+
 def to_bf16(feats):
-    """bf16 shadow of an fp32 feature matrix (cached on the tensor object)."""
+    """bf16 operand rows of an fp32 feature matrix, zero-padded to pcg_tc_cin_padded(C) channels (cached on the tensor)."""
+    if feats.dtype == torch.bfloat16:
+        assert feats.shape[1] == cin_padded(feats.shape[1]) and feats.is_contiguous()
+        return feats
     tag = getattr(feats, "_pcg_bf16", None)
     if tag is not None and tag[1] == feats._version:
         return tag[0]
     f = feats.contiguous()
-    out = torch.empty(f.shape, dtype=torch.bfloat16, device=f.device)
-    call("pcg_f32_to_bf16", ptr(f), ptr(out), f.numel(), stream())
+    n, c = f.shape
+    cp = cin_padded(c)
+    out = torch.empty((n, cp), dtype=torch.bfloat16, device=f.device)
+    call("pcg_f32_to_bf16_rows", ptr(f), n, c, cp, ptr(out), stream())
     feats._pcg_bf16 = (out, feats._version)
     return out
 
@@ -243,15 +255,17 @@ class ConvProfiler:
     """Optional per-launch CUDA-event timing of the convolution kernels (bench.py's roofline pass).
     Events are recorded on torch's current stream, which is the stream the kernels are launched on."""
 
-    def __init__(self):
+    def __init__(self, detail=False):
         self.records = []
         self._pairs = {}
+        self.detail = detail          # also record per-launch row counts and mean active offsets per tile
+        self.launches = []
 
     def pairs(self, nbr):
-        key = nbr.data_ptr()
+        key = id(nbr)                       # the tensor is kept alive below, so the id cannot be recycled
         if key not in self._pairs:
-            self._pairs[key] = int((nbr >= 0).sum().item())
-        return self._pairs[key]
+            self._pairs[key] = (int((nbr >= 0).sum().item()), nbr)
+        return self._pairs[key][0]
 
     def summary(self):
         torch.cuda.synchronize()
@@ -269,56 +283,75 @@ profiler = None      # set to a ConvProfiler() to time every convolution launch
 
 
 def tc_eligible(K, cin, cout):
-    return cin % 8 == 0 and cin >= 32 and cout % 16 == 0 and 16 <= cout <= 256 and K <= 128
+    """Static shape rule (never by timing: determinism).  Everything with a reduction depth worth a
+    tensor-core tile goes to tcgen05; the 1x1 colour head stays fp32 (its output is rounded to 8 bits)."""
+    return K <= 128 and cout <= 256 and K * cin >= 32 and not (K == 1 and cout < 16)
 
 
-def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT_NONE, packed=None, want_bf16=False):
-    """out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); fp32 features in, fp32 out.
+def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT_NONE, packed=None, out="f32"):
+    """out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]).
 
-    weight: (K,cin,cout) or (cin,cout) for K == 1.  Chooses the tcgen05 bf16 kernel when the
-    shape allows (static rule, never by timing: determinism).
+    feats: fp32 (N,cin), or bf16 (N,roundup8(cin)) as produced by a previous call with out="bf16".
+    out: "f32" -> fp32 tensor; "both" -> fp32 tensor carrying a bf16 shadow for the next tensor-core layer;
+    "bf16" -> bf16 tensor only (hidden activations that only feed another convolution).  On the fp32 SIMT path
+    the result is always fp32.  weight: (K,cin,cout) or (cin,cout) for K == 1.
     """
     _need_cuda(feats, "features")
     w3 = weight if weight.dim() == 3 else weight.unsqueeze(0)
     K, cin, cout = w3.shape
-    assert K == ksize ** 3 and feats.shape[1] == cin, f"kernel {tuple(w3.shape)} vs features {tuple(feats.shape)}"
+    assert K == ksize ** 3, f"kernel {tuple(w3.shape)} vs kernel_size {ksize}"
+    if feats.dtype == torch.bfloat16:
+        assert feats.shape[1] == cin_padded(cin), f"kernel {tuple(w3.shape)} vs bf16 features {tuple(feats.shape)}"
+    else:
+        assert feats.shape[1] == cin, f"kernel {tuple(w3.shape)} vs features {tuple(feats.shape)}"
     nbr, tmask = in_set.kernel_map(out_set, ksize, transposed)
     n_out = out_set.n
-    out = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device)
     b = bias.reshape(-1).contiguous() if bias is not None else None
     mode = _conv_mode
-    use_tc = mode != "f32" and tc_eligible(K, cin, cout) and tmask is not None
+    use_tc = mode != "f32" and tc_eligible(K, cin, cout) and tmask is not None and feats.shape[0] > 0
     if mode == "tc" and not use_tc:
         raise RuntimeError(f"conv shape K={K} cin={cin} cout={cout} is not tensor-core eligible")
+    if not use_tc and feats.dtype == torch.bfloat16:
+        raise RuntimeError("bf16 features need the tensor-core path")
     prof = profiler
     if prof is not None:
         pairs = prof.pairs(nbr)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if prof.detail:
+            act_mean = float(sum(((tmask.view(-1).to(torch.int64) & 0xFFFFFFFF) >> i & 1).sum() for i in range(32)).item()) / max(tmask.shape[0], 1) if tmask is not None else float(K)
+            prof.launches.append({"shape": (K, cin, cout), "n_in": int(feats.shape[0]), "n_out": int(n_out), "pairs": pairs,
+                                  "active_per_tile": act_mean, "transposed": bool(transposed), "e": (e0, e1)})
     if use_tc:
         fb = to_bf16(feats)
         wp = (packed or PackedWeights()).get(w3.detach())
+        want_bf16 = out in ("bf16", "both") and cout == cin_padded(cout)
+        want_f32 = out != "bf16" or not want_bf16
+        of = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device) if want_f32 else None
         ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
         if prof is not None:
             e0.record()
-        call("pcg_conv_fwd_tc", ptr(fb), feats.shape[0], cin, ptr(nbr), ptr(tmask), K, n_out, ptr(wp), ptr(b), cout,
-             int(act), ptr(out), ptr(ob), stream())
+        call("pcg_conv_fwd_tc", ptr(fb), feats.shape[0], cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, n_out, ptr(wp), ptr(b), cout,
+             int(act), ptr(of), ptr(ob), stream())
         if prof is not None:
             e1.record()
             prof.records.append(("conv_tc", (K, cin, cout), 2.0 * pairs * cin * cout,
-                                 2.0 * feats.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
+                                 2.0 * feats.shape[0] * cin + (4.0 if want_f32 else 2.0) * n_out * cout, e0, e1))
+        if of is None:
+            return ob
         if ob is not None:
-            out._pcg_bf16 = (ob, out._version)
-    else:
-        f = feats.contiguous()
-        if prof is not None:
-            e0.record()
-        call("pcg_conv_fwd_f32", ptr(f), f.shape[0], cin, ptr(nbr), K, n_out, ptr(w3.detach().contiguous()), ptr(b),
-             cout, int(act), ptr(out), stream())
-        if prof is not None:
-            e1.record()
-            prof.records.append(("conv_f32", (K, cin, cout), 2.0 * pairs * cin * cout,
-                                 4.0 * f.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
-    return out
+            of._pcg_bf16 = (ob, of._version)
+        return of
+    f = feats.contiguous()
+    of = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device)
+    if prof is not None:
+        e0.record()
+    call("pcg_conv_fwd_f32", ptr(f), f.shape[0], cin, ptr(nbr), nbr.shape[1], K, n_out, ptr(w3.detach().contiguous()), ptr(b),
+         cout, int(act), ptr(of), stream())
+    if prof is not None:
+        e1.record()
+        prof.records.append(("conv_f32", (K, cin, cout), 2.0 * pairs * cin * cout,
+                             4.0 * f.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
+    return of
 
 
 def channelwise_conv(feats, cset, kernel, ksize):
@@ -326,7 +359,7 @@ def channelwise_conv(feats, cset, kernel, ksize):
     f = feats.contiguous()
     out = torch.empty_like(f)
     k = kernel.detach().contiguous()
-    call("pcg_channelwise_conv", ptr(f), f.shape[1], ptr(nbr), ksize ** 3, cset.n, ptr(k), k.shape[1], ptr(out), stream())
+    call("pcg_channelwise_conv", ptr(f), f.shape[1], ptr(nbr), nbr.shape[1], ksize ** 3, cset.n, ptr(k), k.shape[1], ptr(out), stream())
     return out
 
 
