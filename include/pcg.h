@@ -119,6 +119,39 @@ int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
 /* n rows of c floats -> n rows of c_padded >= c bf16, zero padded. */
 int pcg_f32_to_bf16_rows(const float *src, long n, int c, int c_padded, void *dst, void *stream);
 
+/* Dense bf16 product on the tensor-core kernel: out_bf16[n][0..n_cols) = feats[n][:] @ Wmat[:, 0..n_cols)
+ * (fp32 accumulation, bf16 result, row pitch n_cols).  Wmat's columns are given in groups of 256: wpacked =
+ * pcg_pack_weights_bf16 of a (G, cin, 256) tensor, G = ceil(n_cols/256), zero padded; n_cols % 16 == 0.
+ * nbr / tile_mask: the identity map over n rows (nbr[0][i] = i, padding -1, tile_mask word 0 = 1).
+ * First half of the GEMM-first generative transposed convolution: T[p][k][:] = F[p] @ W[k] for all k at once
+ * (ME ConvolutionTransposeForwardGPU, ME3, every (parent, offset) pair hits). */
+int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const int32_t *nbr, long nbr_pitch,
+                          const uint32_t *tile_mask, const void *wpacked, long n_cols, void *out_bf16, void *stream);
+
+/* ---- octree-cell generative up-sampling, kernel 5 / stride 2 (ME3; model/transforms.py:129-137) -------------
+ * Children (stride ts_out = ts/2) of parents (stride ts) grouped by CELL = ts-aligned cube of <= 8 children, child
+ * bit b = bx + 2 by + 4 bz.  Build order:
+ *   1. cells       = pcg_generate_coords(parents, ksize 3, stride 1, ts_out = ts)     (+ the cell table)
+ *   2. pnbr        = pcg_kernel_map(parent table, cells, ksize 3, ts, transposed 0)   (27 x pitch(n_cells))
+ *   3. pcg_cells_info  -> cell_mask (existing children), cell_base (first child row), *d_n_out (number of children)
+ *   4. pcg_cells_emit  -> child coordinates (cell-major, bit order) and out_cell (cell of every child)
+ * The child SET equals ME's unique{p + off*ts_out : off in [-2,2]^3}; the row order is libpcg's own. */
+size_t pcg_cells_scratch_bytes(long n_cells);
+int pcg_cells_info(const int32_t *pnbr, long pnbr_pitch, long n_cells, uint8_t *cell_mask, int32_t *cell_base,
+                   int32_t *d_n_out, void *scratch, size_t scratch_bytes, void *stream);
+int pcg_cells_emit(const int32_t *cell_coords, const uint8_t *cell_mask, const int32_t *cell_base, long n_cells, int ts_out,
+                   int32_t *out_coords, int32_t *out_cell, void *stream);
+/* 3x3x3 stride-1 kernel map of the children among themselves -- identical to pcg_kernel_map over a table of the
+ * children, derived from 7 probes of the (8x smaller) cell table per child. */
+int pcg_cells_kernel_map3(const uint64_t *cell_keys, const int32_t *cell_vals, long cell_cap, const int32_t *out_coords,
+                          const int32_t *out_cell, long n_out, int ts_out, const uint8_t *cell_mask, const int32_t *cell_base,
+                          int32_t *nbr, long nbr_pitch, uint32_t *tile_mask, void *stream);
+/* Second half of the GEMM-first transposed convolution: out[child] = act(bias + sum_e T[pnbr[e][cell]][k(b - 2e)][:]),
+ * e ascending over the parents that reach the child (fixed order, fp32 accumulation).  T: bf16 [n_parents][125][cout]. */
+int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const int32_t *out_coords,
+                     const int32_t *out_cell, long n_out, int ts_out, const float *bias, int act, float *out_f32,
+                     void *out_bf16, void *stream);
+
 /* Channel-wise convolution out[o][c] = sum_i F[nbr[i][o]][c] * w[i][c or 0]
  * (ME.MinkowskiChannelwiseConvolution, loss.py:185-188; w_cols = C or 1). */
 int pcg_channelwise_conv(const float *feats, int c, const int32_t *nbr, long nbr_pitch, int K, long n_out,

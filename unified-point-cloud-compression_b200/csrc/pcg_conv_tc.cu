@@ -128,6 +128,9 @@ struct TcParams {
     int stages;
     int tmem_cols;   // power of two >= max(32, cout_p)
     int act;
+    long out_ld;     // output row pitch in elements (== cout unless grouped)
+    int cout_total;  // grouped mode (gridDim.y > 1): CTA (x, g) computes output columns [g*cout_p, min((g+1)*cout_p, cout_total))
+                     // with the weight slice k = g (K must be 1): a dense [n_out x cin] @ [cin x cout_total] product
 };
 
 template <int RB>
@@ -151,6 +154,9 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long tile = blockIdx.x;
+    const int group = blockIdx.y;
+    const int col0 = group * p.cout_p;
+    const int cout_here = (p.cout_total - col0) < p.cout ? (p.cout_total - col0) : p.cout;
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             for (int g = 0; g < G; ++g)
                 if (g < subs) tma_gather4(a_base + g * SUB_A + (uint32_t)lane * 4u * RB, &tm, cc * TC_KCHUNK, idx[g], fb);
             if (lane < subs) {
-                const int k = RB == 128 ? active[a] : active[it * G + lane];
+                const int k = (RB == 128 ? active[a] : active[it * G + lane]) + group;
                 bulk_g2s(a_base + TC_A_BYTES + lane * sub_b, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
             }
             // advance this warp's cursor by P items and prefetch the next item's neighbour indices
@@ -240,7 +246,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             tc_fence_after();
         }
         const uint32_t lane_base = tmem_d + ((uint32_t)(warp * 32) << 16);
-        for (int c0 = 0; c0 < p.cout; c0 += 16) {
+        for (int c0 = 0; c0 < cout_here; c0 += 16) {
             uint32_t v[16];
             if (n_items > 0) tmem_ld16(lane_base + (uint32_t)c0, v);
             else {
@@ -251,10 +257,10 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                 float f[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
-                if ((p.cout & 15) == 0) {
+                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < cout_here) ? __ldg(p.bias + col0 + c0 + j) : 0.f), p.act);
+                if ((cout_here & 15) == 0) {
                     if (p.out_f32) {
-                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
+                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.out_ld + col0 + c0);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
                     }
@@ -265,14 +271,14 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                             __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
                             pk[j] = *reinterpret_cast<uint32_t *>(&h);
                         }
-                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
+                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.out_ld + col0 + c0);
                         dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                         dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                     }
                 } else if (p.out_f32) {   // narrow heads (cout = 1, 3, ...): scalar stores of the real columns
 #pragma unroll
                     for (int j = 0; j < 16; ++j)
-                        if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
+                        if (c0 + j < cout_here) p.out_f32[o * p.out_ld + col0 + c0 + j] = f[j];
                 }
             }
         }
@@ -377,16 +383,16 @@ static PcgEncodeTiled tensor_map_encoder() {
 extern "C" int pcg_tc_cin_padded(int cin) { return tc_cin_p(cin); }
 
 template <int RB>
-static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cudaStream_t st) {
+static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, int groups, cudaStream_t st) {
     PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_tc<RB><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
+    k_conv_tc<RB><<<dim3((unsigned)cdiv(p.n_out, TC_ROWS), (unsigned)groups), 160, smem, st>>>(tm, p);
     PCG_LAUNCHED();
     return 0;
 }
 
-extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
-                               int act, float *out_f32, void *out_bf16, void *stream) {
+static int conv_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                        const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                        int act, float *out_f32, void *out_bf16, long out_ld, int cout_total, int groups, void *stream) {
     PCG_CHECK_ARG(cin >= 1 && cin <= 1024, "pcg_conv_fwd_tc: cin=%d", cin);
     PCG_CHECK_ARG(cout >= 1 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be in [1,256]", cout);
     PCG_CHECK_ARG(out_bf16 == nullptr || (cout & 15) == 0, "pcg_conv_fwd_tc: a bf16 output needs cout %% 16 == 0 (cout=%d)", cout);
@@ -418,6 +424,7 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.n_out = n_out; p.cout = cout; p.cout_p = tc_cout_p(cout); p.K = K;
     p.chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
     p.act = act;
+    p.out_ld = out_ld; p.cout_total = cout_total;
     p.tmem_cols = 32;
     while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
     const size_t stage_bytes = TC_A_BYTES + (size_t)p.cout_p * 128;
@@ -427,7 +434,27 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
     cudaStream_t st = as_stream(stream);
-    if (rb == 32) return launch_tc<32>(tm, p, smem, st);
-    if (rb == 64) return launch_tc<64>(tm, p, smem, st);
-    return launch_tc<128>(tm, p, smem, st);
+    if (rb == 32) return launch_tc<32>(tm, p, smem, groups, st);
+    if (rb == 64) return launch_tc<64>(tm, p, smem, groups, st);
+    return launch_tc<128>(tm, p, smem, groups, st);
+}
+
+extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                               int act, float *out_f32, void *out_bf16, void *stream) {
+    return conv_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
+                        cout, cout, 1, stream);
+}
+
+// Dense product on the same kernel: out_bf16[n][0..n_cols) = feats[n][:] @ Wmat[:, 0..n_cols), n_cols a multiple of 16.
+// wpacked = pcg_pack_weights_bf16 of a (G, cin, 256) tensor holding Wmat's columns in groups of 256 (zero padded),
+// G = ceil(n_cols / 256).  CTA (tile, g) computes one 128 x 256 block.  nbr/tile_mask: the identity map over n rows
+// (nbr[0][i] = i, padding -1; tile_mask word 0 = 1).
+extern "C" int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const int32_t *nbr, long nbr_pitch,
+                                     const uint32_t *tile_mask, const void *wpacked, long n_cols, void *out_bf16, void *stream) {
+    PCG_CHECK_ARG(n_cols >= 16 && (n_cols & 15) == 0 && n_cols < (1L << 30), "pcg_gemm_bf16_grouped: n_cols=%ld must be a multiple of 16", n_cols);
+    const int groups = (int)cdiv(n_cols, 256);
+    PCG_CHECK_ARG(groups <= 65535, "pcg_gemm_bf16_grouped: too many column groups (%d)", groups);
+    return conv_tc_impl(feats_bf16, n, cin, nbr, nbr_pitch, tile_mask, 1, n, wpacked, nullptr, 256, PCG_ACT_NONE, nullptr, out_bf16,
+                        n_cols, (int)n_cols, groups, stream);
 }
