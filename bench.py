@@ -208,15 +208,22 @@ def main():
 
     def timed(fn, steps):
         total = 0.0
+        per_step = []
+        host_ms = []
         for _ in range(steps):
             flush.fill_(1)                                   # evict L2 between timed iterations
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
+            t0 = time.perf_counter()
             fn()
+            host_ms.append(1e3 * (time.perf_counter() - t0))     # host enqueue time (includes the step's own syncs)
             e1.record()
             flush[:1].fill_(2)                               # 1-block marker launch: end of the step in an ncu launch list
             torch.cuda.synchronize()
-            total += e0.elapsed_time(e1)
+            per_step.append(e0.elapsed_time(e1))
+            total += per_step[-1]
+        print(f"[bench] {fn.__name__} per-step ms: " + " ".join(f"{t:.2f}" for t in per_step) +
+              " | host enqueue ms: " + " ".join(f"{t:.2f}" for t in host_ms), file=sys.stderr)
         return total
 
     with torch.no_grad():

@@ -119,14 +119,23 @@ int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
 /* n rows of c floats -> n rows of c_padded >= c bf16, zero padded. */
 int pcg_f32_to_bf16_rows(const float *src, long n, int c, int c_padded, void *dst, void *stream);
 
-/* Dense bf16 product on the tensor-core kernel: out_bf16[n][0..n_cols) = feats[n][:] @ Wmat[:, 0..n_cols)
- * (fp32 accumulation, bf16 result, row pitch n_cols).  Wmat's columns are given in groups of 256: wpacked =
- * pcg_pack_weights_bf16 of a (G, cin, 256) tensor, G = ceil(n_cols/256), zero padded; n_cols % 16 == 0.
- * nbr / tile_mask: the identity map over n rows (nbr[0][i] = i, padding -1, tile_mask word 0 = 1).
+/* Narrow occupancy-head layers on bf16 rows gathered by 8/16-byte loads straight into mma.sync A fragments
+ * (csrc/pcg_conv_narrow.cu; model/transforms.py:146-160).  Same arithmetic contract as pcg_conv_fwd_tc (bf16 operands,
+ * fp32 accumulation, fixed order).  C_in <= 64 (rows of pcg_tc_cin_padded(cin) bf16), C_out <= 16; wfrag from
+ * pcg_pack_weights_mma; out_bf16 (optional) is written as rows of 16 bf16, zero padded. */
+size_t pcg_mma_weight_bytes(int K, int cin, int cout);
+int pcg_pack_weights_mma(const float *weight, int K, int cin, int cout, void *wfrag, void *stream);
+int pcg_conv_fwd_mma(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch, int K, long n_out,
+                     const void *wfrag, const float *bias, int cout, int act, float *out_f32, void *out_bf16, void *stream);
+
+/* Dense bf16 product on tcgen05 (csrc/pcg_gemm_tc.cu): out_bf16[n][0..n_cols) = feats[n][:] @ Wmat[:, 0..n_cols)
+ * (fp32 accumulation in TMEM, bf16 result, row pitch n_cols).  feats_bf16: n rows of roundup64(cin) bf16, 33 <= cin <= 128.
+ * Wmat's columns are given in groups of 256: wpacked = pcg_pack_weights_bf16 of a (G, cin, 256) tensor,
+ * G = ceil(n_cols/256), zero padded; n_cols % 16 == 0.
  * First half of the GEMM-first generative transposed convolution: T[p][k][:] = F[p] @ W[k] for all k at once
- * (ME ConvolutionTransposeForwardGPU, ME3, every (parent, offset) pair hits). */
-int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const int32_t *nbr, long nbr_pitch,
-                          const uint32_t *tile_mask, const void *wpacked, long n_cols, void *out_bf16, void *stream);
+ * (ME ConvolutionTransposeForwardGPU, ME3: every (parent, offset) pair hits, so nothing needs gathering). */
+int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const void *wpacked, long n_cols, void *out_bf16,
+                          void *stream);
 
 /* ---- octree-cell generative up-sampling, kernel 5 / stride 2 (ME3; model/transforms.py:129-137) -------------
  * Children (stride ts_out = ts/2) of parents (stride ts) grouped by CELL = ts-aligned cube of <= 8 children, child
@@ -147,10 +156,11 @@ int pcg_cells_kernel_map3(const uint64_t *cell_keys, const int32_t *cell_vals, l
                           const int32_t *out_cell, long n_out, int ts_out, const uint8_t *cell_mask, const int32_t *cell_base,
                           int32_t *nbr, long nbr_pitch, uint32_t *tile_mask, void *stream);
 /* Second half of the GEMM-first transposed convolution: out[child] = act(bias + sum_e T[pnbr[e][cell]][k(b - 2e)][:]),
- * e ascending over the parents that reach the child (fixed order, fp32 accumulation).  T: bf16 [n_parents][125][cout]. */
-int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const int32_t *out_coords,
-                     const int32_t *out_cell, long n_out, int ts_out, const float *bias, int act, float *out_f32,
-                     void *out_bf16, void *stream);
+ * e ascending over the parents that reach the child (fixed order, fp32 accumulation).  T: bf16 [n_parents][125][cout],
+ * cout in {32, 64, 128, 256}.  Child rows are addressed through cell_base / cell_mask (row = base + rank of bit b). */
+int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const uint8_t *cell_mask,
+                     const int32_t *cell_base, long n_cells, const float *bias, int act, float *out_f32, void *out_bf16,
+                     void *stream);
 
 /* Channel-wise convolution out[o][c] = sum_i F[nbr[i][o]][c] * w[i][c or 0]
  * (ME.MinkowskiChannelwiseConvolution, loss.py:185-188; w_cols = C or 1). */

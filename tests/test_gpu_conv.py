@@ -47,6 +47,7 @@ def test_conv_matches_oracle(pkg, dev, cin, cout, ksize, stride, transposed):
     modes = [("f32", 2e-5)]
     if so.tc_eligible(K, cin, cout):
         modes.append(("tc", 1e-2))
+        modes.append(("auto", 1e-2))          # narrow heads take the register-gather kernels (dot / mma32) here
     for mode, tol in modes:
         prev = so.set_conv_mode(mode)
         try:
@@ -65,18 +66,19 @@ def test_tc_path_is_exact_on_bf16_representable_inputs(pkg, dev):
     C, cs = setup(dev, pkg, seed=11)
     rng = np.random.default_rng(0)
     for cin, cout, ksize in ((64, 32, 3), (128, 128, 3), (192, 256, 3), (32, 16, 3), (16, 1, 3), (8, 24, 3), (4, 32, 5),
-                            (40, 48, 3), (64, 1, 3), (3, 5, 3)):
+                            (40, 48, 3), (64, 1, 3), (3, 5, 3), (128, 1, 3), (24, 9, 3), (32, 1, 5), (20, 16, 5)):
         Fm = rng.integers(-4, 5, (len(C), cin)).astype(np.float32)
         W = rng.integers(-2, 3, (ksize ** 3, cin, cout)).astype(np.float32)
         b = rng.integers(-3, 4, (1, cout)).astype(np.float32)
         ref = oracle_conv(C, C, Fm, W, b, ksize, 1, False)
-        prev = so.set_conv_mode("tc")
-        try:
-            out = so.sparse_conv(torch.from_numpy(Fm).to(dev), cs, cs, torch.from_numpy(W).to(dev),
-                                 torch.from_numpy(b).to(dev), ksize, False)
-        finally:
-            so.set_conv_mode(prev)
-        assert np.array_equal(out.cpu().numpy(), ref), f"cin={cin} cout={cout}: max |d| = {np.abs(out.cpu().numpy() - ref).max()}"
+        for mode in ("tc", "auto"):
+            prev = so.set_conv_mode(mode)
+            try:
+                out = so.sparse_conv(torch.from_numpy(Fm).to(dev), cs, cs, torch.from_numpy(W).to(dev),
+                                     torch.from_numpy(b).to(dev), ksize, False)
+            finally:
+                so.set_conv_mode(prev)
+            assert np.array_equal(out.cpu().numpy(), ref), f"{mode} cin={cin} cout={cout}: max |d| = {np.abs(out.cpu().numpy() - ref).max()}"
 
 
 @pytest.mark.parametrize("mode", ["f32", "tc"])
@@ -165,3 +167,34 @@ def test_topk_selection_consistent_with_fp32_logits(pkg, dev):
     exact = np.zeros(n, bool)
     exact[np.argsort(-ref, kind="stable")[:k]] = True
     print(f"top-k agreement with the fp32 selection: {(mask & exact).sum() / k:.4f} (error band {band:.2e}, logit std {ref.std():.2e})")
+
+
+@pytest.mark.parametrize("cin,cout,kind", [(128, 128, "surface"), (128, 32, "surface"), (64, 32, "scattered"), (64, 64, "surface")])
+def test_gen_conv_transpose_cells_matches_oracle(pkg, dev, cin, cout, kind):
+    """Kernel-5/stride-2 generative transposed convolution on the octree-cell path (GEMM-first + gather-reduce) vs the
+    fp32 oracle on the same coordinates, compared row by row."""
+    so = pkg.sparse_ops
+    ts = 2
+    if kind == "surface":
+        C, cs = setup(dev, pkg, seed=cin + cout, ts=ts)
+    else:
+        C = synth.random_cloud(3, 800, 50, batch=1)
+        C[:, 1:] *= ts
+        cs = so.CoordSet(torch.from_numpy(C).to(dev), ts)
+    out_set = cs.generated_cells()
+    C_out = out_set.coords.cpu().numpy()
+    rng = np.random.default_rng(cin + 3 * cout)
+    Fm = rng.standard_normal((len(C), cin)).astype(np.float32)
+    W = (rng.standard_normal((125, cin, cout)) / np.sqrt(cin * 125) * 6).astype(np.float32)
+    b = rng.standard_normal((1, cout)).astype(np.float32)
+    ref = oracle_conv(C, C_out, Fm, W, b, 5, 1, True, act=1)
+    out = so.gen_conv_transpose_cells(torch.from_numpy(Fm).to(dev), cs, out_set, torch.from_numpy(W).to(dev),
+                                      torch.from_numpy(b).to(dev), act=so.ACT_RELU, out="both")
+    err = rel_l2(out.cpu().numpy(), ref)
+    assert err < 1e-2, f"rel-L2 {err:.3e}"
+    shadow = out._pcg_bf16[0].float().cpu().numpy()
+    assert rel_l2(shadow, ref) < 1.2e-2
+    # run-to-run bit reproducibility (fact 9)
+    again = so.gen_conv_transpose_cells(torch.from_numpy(Fm).to(dev), cs, out_set, torch.from_numpy(W).to(dev),
+                                        torch.from_numpy(b).to(dev), act=so.ACT_RELU, out="f32")
+    assert torch.equal(out, again)

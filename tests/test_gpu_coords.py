@@ -186,3 +186,65 @@ def test_features_at(pkg, dev):
         out = so.features_at(Fm.to(dev), cs, torch.from_numpy(q).to(dev)).cpu()
         ref = x.features_at_coordinates(torch.from_numpy(q))
         assert (out - ref).abs().max() <= tol
+
+
+# ---------------------------------------------------------------------------- octree-cell generative path
+@pytest.mark.parametrize("ts,kind", [(2, "surface"), (4, "surface"), (8, "scattered"), (2, "batch2")])
+def test_generated_cells_match_oracle_set_and_generic_maps(pkg, dev, ts, kind):
+    """Cell-organised kernel-5/stride-2 candidates: the SET is ME's (oracle), rows are unique, the 3x3x3 map derived
+    from the cells equals the hash-built map over the same rows, and the per-cell parent lists reproduce the
+    transposed kernel map."""
+    so = pkg.sparse_ops
+    if kind == "surface":
+        pts, _ = synth.small_cloud(seed=7)
+        C = np.concatenate([np.zeros((len(pts), 1), np.int32), pts * ts], axis=1)
+    elif kind == "scattered":
+        C = cloud(9, n=700, extent=60)
+        C[:, 1:] *= ts
+    else:
+        C = cloud(11, batch=2, n=900, extent=25)
+        C[:, 1:] *= ts
+        C[:5, 1:] = -C[:5, 1:]                      # negative coordinates: floor-to-cell must stay correct
+        C = C[np.unique(me_ref.pack_keys(C), return_index=True)[1]]
+    cs = so.CoordSet(to_dev(C, dev), ts)
+    out = cs.generated_cells()
+    ts_out = ts // 2
+    ref = me_ref.generate_coords(C, ts_out, 5)
+    got = out.coords.cpu().numpy()
+    assert out.n == len(ref) and (np.sort(me_ref.pack_keys(got)) == np.sort(me_ref.pack_keys(ref))).all()
+    assert len(np.unique(me_ref.pack_keys(got))) == len(got)
+    # 3x3x3 map among the children: cells vs hash
+    nbr_c, tm_c = out.kernel_map(out, 3, False)
+    plain = so.CoordSet(out.coords.clone(), ts_out)
+    nbr_h, tm_h = plain.kernel_map(plain, 3, False)
+    assert torch.equal(nbr_c, nbr_h)
+    assert torch.equal(tm_c, tm_h)
+    # parent lists: child row r at cell c, bit b gets parent pnbr[e][c] through offset b - 2e
+    ref_t = me_ref.neighbour_table(C, got, 5, ts_out, True)           # [125][n_out] parent rows
+    pn = out.pnbr.cpu().numpy()
+    cell = out.out_cell.cpu().numpy()[:out.n]
+    cc = out.cells.coords.cpu().numpy()[cell]
+    b = (got[:, 1:] - cc[:, 1:]) // ts_out
+    assert ((b >= 0) & (b <= 1)).all()
+    rebuilt = np.full_like(ref_t, -1)
+    for ez in (-1, 0, 1):
+        for ey in (-1, 0, 1):
+            for ex in (-1, 0, 1):
+                e = (ex + 1) + 3 * (ey + 1) + 9 * (ez + 1)
+                off = b - 2 * np.array([ex, ey, ez])
+                ok = (np.abs(off) <= 2).all(axis=1)
+                k = (off[:, 0] + 2) + 5 * (off[:, 1] + 2) + 25 * (off[:, 2] + 2)
+                rows = np.nonzero(ok)[0]
+                rebuilt[k[rows], rows] = pn[e, cell[rows]]
+    assert (rebuilt == ref_t).all()
+
+
+def test_generated_cells_empty_and_single(pkg, dev):
+    so = pkg.sparse_ops
+    one = so.CoordSet(to_dev(np.array([[0, 4, 8, -4]]), dev), 4).generated_cells()
+    assert one.n == 125 and one.ts == 2
+    nbr, _ = one.kernel_map(one, 3, False)
+    plain = so.CoordSet(one.coords.clone(), 2)
+    assert torch.equal(nbr, plain.kernel_map(plain, 3, False)[0])
+    empty = so.CoordSet(torch.zeros((0, 4), dtype=torch.int32, device=dev), 4).generated_cells()
+    assert empty.n == 0 and empty.coords.shape == (0, 4)

@@ -125,6 +125,7 @@ class MinkowskiConvolutionBase(nn.Module):
         self.kernel = nn.Parameter(torch.empty(*shape))
         self.bias = nn.Parameter(torch.empty(1, self.out_channels)) if bias else None
         self._packed = so.PackedWeights()
+        self._packed_gemm = so.PackedGemmWeights()
         self.fused_activation = so.ACT_NONE      # host mirror may fuse the following (Leaky)ReLU into the epilogue
         self.emit = "f32"                        # "both": also write the bf16 shadow the next tensor-core layer reads
         self.reset_parameters()
@@ -143,9 +144,16 @@ class MinkowskiConvolutionBase(nn.Module):
         if input.F.shape[1] != self.in_channels:
             raise RuntimeError(f"expected {self.in_channels} input channels, got {input.F.shape[1]}")
         in_set = input.coord_set
+        grad = torch.is_grad_enabled() and (input.F.requires_grad or self.kernel.requires_grad and self.training)
         if not self.is_transpose:
             out_set = in_set.strided(self.stride)
         elif self.expand_coordinates:
+            if not grad and so.cells_eligible(self.kernel_size, self.stride, self.in_channels, self.out_channels):
+                # kernel 5 / stride 2: octree-cell candidate set + GEMM-first transposed convolution
+                out_set = in_set.generated_cells()
+                out = so.gen_conv_transpose_cells(input.F, in_set, out_set, self.kernel, self.bias, act=self.fused_activation,
+                                                  packed=self._packed_gemm, out=self.emit)
+                return SparseTensor(out, _coord_set=out_set)
             out_set = in_set.generated(self.kernel_size, self.stride)
         else:
             if coordinates is None:
@@ -159,7 +167,7 @@ class MinkowskiConvolutionBase(nn.Module):
                     device=input.device).coord_set
             if out_set.ts != ts_out:
                 raise RuntimeError(f"output coordinates have tensor stride {out_set.ts}, expected {ts_out}")
-        if torch.is_grad_enabled() and (input.F.requires_grad or self.kernel.requires_grad and self.training):
+        if grad:
             from ..autograd import sparse_conv_autograd
             out = sparse_conv_autograd(input.F, in_set, out_set, self.kernel, self.bias, self.kernel_size,
                                        self.is_transpose, self.fused_activation)

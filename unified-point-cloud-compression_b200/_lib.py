@@ -35,12 +35,15 @@ _PROTOS = {
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),
     "pcg_pack_weights_bf16": (_I, [_P, _I, _I, _I, _P, _P]),
     "pcg_conv_fwd_tc": (_I, [_P, _L, _I, _P, _L, _P, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
-    "pcg_gemm_bf16_grouped": (_I, [_P, _L, _I, _P, _L, _P, _P, _L, _P, _P]),
+    "pcg_mma_weight_bytes": (_SZ, [_I, _I, _I]),
+    "pcg_pack_weights_mma": (_I, [_P, _I, _I, _I, _P, _P]),
+    "pcg_conv_fwd_mma": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
+    "pcg_gemm_bf16_grouped": (_I, [_P, _L, _I, _P, _L, _P, _P]),
     "pcg_cells_scratch_bytes": (_SZ, [_L]),
     "pcg_cells_info": (_I, [_P, _L, _L, _P, _P, _P, _P, _SZ, _P]),
     "pcg_cells_emit": (_I, [_P, _P, _P, _L, _I, _P, _P, _P]),
     "pcg_cells_kernel_map3": (_I, [_P, _P, _L, _P, _P, _L, _I, _P, _P, _P, _L, _P, _P]),
-    "pcg_cells_reduce": (_I, [_P, _I, _P, _L, _P, _P, _L, _I, _P, _I, _P, _P, _P]),
+    "pcg_cells_reduce": (_I, [_P, _I, _P, _L, _P, _P, _L, _P, _I, _P, _P, _P]),
     "pcg_f32_to_bf16": (_I, [_P, _P, _L, _P]),
     "pcg_f32_to_bf16_rows": (_I, [_P, _L, _I, _I, _P, _P]),
     "pcg_channelwise_conv": (_I, [_P, _I, _P, _L, _I, _L, _P, _I, _P, _P]),

@@ -188,49 +188,65 @@ extern "C" int pcg_cells_kernel_map3(const uint64_t *cell_keys, const int32_t *c
 
 // ---------------------------------------------------------------------------- gather-reduce of the per-parent products
 // out[child] = act(bias + sum_{e valid} T[pnbr[e][cell]][k(b - 2e)][:]), e ascending: one fixed-order fp32 chain per element.
-// LANES = cout / 8 lanes per child, each owning 8 channels (one 16-byte load per parent).
+// Cell-centric: the 8 child slots of a cell x LANES = cout/8 lanes (8 channels = one 16-byte load each) are adjacent
+// threads, a warp covers 32/LANES child slots of ONE cell.  The warp reads the cell's 27 parent rows once (lane e loads
+// pnbr[e][cell]), ballots which parents exist and walks only those -- a warp-uniform loop, four parents per batch so
+// that four independent 16-byte loads of T are in flight per lane; whether parent e reaches child b is a per-lane
+// predicate, not a branch.
 template <int LANES>
 __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__restrict__ T, int cout, const int32_t *__restrict__ pnbr,
-                                                      long pitch, const int32_t *__restrict__ out_coords,
-                                                      const int32_t *__restrict__ out_cell, long n_out, int ts_out,
+                                                      long pitch, const uint8_t *__restrict__ cell_mask,
+                                                      const int32_t *__restrict__ cell_base, long n_cells,
                                                       const float *__restrict__ bias, int act, float *__restrict__ out_f32,
                                                       __nv_bfloat16 *__restrict__ out_bf16) {
-    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long o = t / LANES;
-    const int part = (int)(t % LANES);
-    if (o >= n_out) return;
-    const int4 c = pcg_ld_coord(out_coords, o);
-    const int ts_in = 2 * ts_out;
-    const int bx = (c.y - pcg_floor_to(c.y, ts_in)) / ts_out, by = (c.z - pcg_floor_to(c.z, ts_in)) / ts_out,
-              bz = (c.w - pcg_floor_to(c.w, ts_in)) / ts_out;
-    const long cell = __ldg(out_cell + o);
+    constexpr int CPW = 32 / LANES;                 // child slots per warp
+    constexpr int WPC = 8 / CPW;                    // warps per cell
+    const int lane = threadIdx.x & 31;
+    const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long cell = gw / WPC;
+    if (cell >= n_cells) return;                    // warp-uniform
+    const int b = (int)(gw % WPC) * CPW + lane / LANES;
+    const int part = lane % LANES;
+    const int bx = b & 1, by = (b >> 1) & 1, bz = (b >> 2) & 1;
+    const int my_prow = lane < 27 ? __ldg(pnbr + (long)lane * pitch + cell) : -1;
+    uint32_t present = __ballot_sync(0xffffffffu, my_prow >= 0);
+    const uint32_t cmask = cell_mask[cell];
+    const bool exists = (cmask >> b) & 1u;
+    const uint32_t reach = exists ? cells_valid_e(b) : 0u;      // parents e that reach child b
     const long t_row = (long)125 * cout;
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    while (present) {
+        int e[4], pr[4];
+        uint4 v[4];
 #pragma unroll
-    for (int ez = -1; ez <= 1; ++ez) {
-        if (bz && ez < 0) continue;
+        for (int u = 0; u < 4; ++u) {
+            e[u] = present ? __ffs(present) - 1 : 31;
+            present &= present - 1;
+            pr[u] = __shfl_sync(0xffffffffu, my_prow, e[u]);        // lane 31 holds -1
+        }
 #pragma unroll
-        for (int ey = -1; ey <= 1; ++ey) {
-            if (by && ey < 0) continue;
+        for (int u = 0; u < 4; ++u) {
+            const int ex = e[u] % 3 - 1, ey = (e[u] / 3) % 3 - 1, ez = e[u] / 9 - 1;
+            const int k = (bx - 2 * ex + 2) + 5 * (by - 2 * ey + 2) + 25 * (bz - 2 * ez + 2);
+            const bool ok = pr[u] >= 0 && ((reach >> e[u]) & 1u);
+            v[u] = ok ? __ldg(reinterpret_cast<const uint4 *>(T + (long)pr[u] * t_row + (long)k * cout) + part) : make_uint4(0, 0, 0, 0);
+            if (!ok) pr[u] = -1;
+        }
 #pragma unroll
-            for (int ex = -1; ex <= 1; ++ex) {
-                if (bx && ex < 0) continue;
-                const int e = (ex + 1) + 3 * (ey + 1) + 9 * (ez + 1);
-                const int prow = __ldg(pnbr + (long)e * pitch + cell);
-                if (prow < 0) continue;
-                const int k = (bx - 2 * ex + 2) + 5 * (by - 2 * ey + 2) + 25 * (bz - 2 * ez + 2);
-                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(T + (long)prow * t_row + (long)k * cout) + part);
-                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        for (int u = 0; u < 4; ++u) {
+            if (pr[u] < 0) continue;                // absent / non-reaching parents add nothing
+            const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    acc[2 * j] += __uint_as_float(w[j] << 16);
-                    acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
-                }
+            for (int j = 0; j < 4; ++j) {
+                acc[2 * j] += __uint_as_float(w[j] << 16);
+                acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
             }
         }
     }
+    if (!exists) return;
+    const long o = (long)__ldg(cell_base + cell) + __popc(cmask & ((1u << b) - 1u));
     const int c0 = part * 8;
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = pcg_apply_act(acc[j] + (bias ? __ldg(bias + c0 + j) : 0.f), act);
@@ -250,22 +266,19 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
     }
 }
 
-extern "C" int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const int32_t *out_coords,
-                                const int32_t *out_cell, long n_out, int ts_out, const float *bias, int act, float *out_f32,
-                                void *out_bf16, void *stream) {
-    PCG_CHECK_ARG(cout == 8 || cout == 16 || cout == 32 || cout == 64 || cout == 128 || cout == 256,
-                  "pcg_cells_reduce: cout=%d must be 8, 16, 32, 64, 128 or 256", cout);
+extern "C" int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const uint8_t *cell_mask,
+                                const int32_t *cell_base, long n_cells, const float *bias, int act, float *out_f32, void *out_bf16,
+                                void *stream) {
+    PCG_CHECK_ARG(cout == 32 || cout == 64 || cout == 128 || cout == 256, "pcg_cells_reduce: cout=%d must be 32, 64, 128 or 256", cout);
     PCG_CHECK_ARG(((uintptr_t)t_bf16 & 15) == 0, "pcg_cells_reduce: T must be 16-byte aligned");
-    if (n_out <= 0) return 0;
+    if (n_cells <= 0) return 0;
     cudaStream_t st = as_stream(stream);
     const __nv_bfloat16 *T = reinterpret_cast<const __nv_bfloat16 *>(t_bf16);
     __nv_bfloat16 *ob = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
     const int lanes = cout / 8;
-    const unsigned blocks = (unsigned)cdiv(n_out * lanes, 256);
-#define PCG_REDUCE(L) k_cells_reduce<L><<<blocks, 256, 0, st>>>(T, cout, pnbr, pnbr_pitch, out_coords, out_cell, n_out, ts_out, bias, act, out_f32, ob)
+    const unsigned blocks = (unsigned)cdiv(n_cells * 8 * lanes, 256);
+#define PCG_REDUCE(L) k_cells_reduce<L><<<blocks, 256, 0, st>>>(T, cout, pnbr, pnbr_pitch, cell_mask, cell_base, n_cells, bias, act, out_f32, ob)
     switch (lanes) {
-        case 1: PCG_REDUCE(1); break;
-        case 2: PCG_REDUCE(2); break;
         case 4: PCG_REDUCE(4); break;
         case 8: PCG_REDUCE(8); break;
         case 16: PCG_REDUCE(16); break;

@@ -16,104 +16,13 @@
 // offsets.  Kernel offsets no row of the tile uses are skipped (tile_mask from pcg_kernel_map).  Every output element
 // is one fixed-order chain of MMAs over ascending (k, cin-chunk): bit-reproducible, and independent of which
 // tile a row lands in (absent neighbours contribute exact zeros).
-#include <cuda.h>
-
-#include "pcg_common.cuh"
+#include "pcg_tc.cuh"
 
 #define TC_ROWS 128
 #define TC_KCHUNK 64                       // bf16 elements per 128-byte swizzled row
 #define TC_A_BYTES (TC_ROWS * 128)         // 16 KiB per stage
 #define TC_LAG 2                           // cp.async groups in flight per producer thread
 #define TC_MAX_STAGES 6
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// K-major SWIZZLE_128B shared-memory matrix descriptor (rows of 128 B, 8-row groups 1024 B apart)
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);  // start address
-    d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;         // stride byte offset between 8-row groups
-    d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
-    return d;
-}
-
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major swizzled shared-memory matrix descriptor for rows of RB bytes (8-row groups 8*RB bytes apart)
-template <int RB>
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-    constexpr uint64_t layout = RB == 128 ? 2 : (RB == 64 ? 4 : 6);   // SWIZZLE_128B / 64B / 32B
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);  // start address
-    d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)((8 * RB) >> 4) << 32;     // stride byte offset between 8-row groups
-    d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
-    d |= layout << 61;
-    return d;
-}
-
-// four feature rows (row indices r.x..r.w, column `col`) -> four consecutive operand rows at `dst`
-__device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap *tm, int col, int4 r, uint32_t bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
-        ::"r"(dst), "l"(tm), "r"(col), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(bar)
-        : "memory");
-}
 
 struct TcParams {
     const int32_t *nbr;           // [K][nbr_pitch], padding entries -1
@@ -128,9 +37,6 @@ struct TcParams {
     int stages;
     int tmem_cols;   // power of two >= max(32, cout_p)
     int act;
-    long out_ld;     // output row pitch in elements (== cout unless grouped)
-    int cout_total;  // grouped mode (gridDim.y > 1): CTA (x, g) computes output columns [g*cout_p, min((g+1)*cout_p, cout_total))
-                     // with the weight slice k = g (K must be 1): a dense [n_out x cin] @ [cin x cout_total] product
 };
 
 template <int RB>
@@ -154,9 +60,6 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long tile = blockIdx.x;
-    const int group = blockIdx.y;
-    const int col0 = group * p.cout_p;
-    const int cout_here = (p.cout_total - col0) < p.cout ? (p.cout_total - col0) : p.cout;
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
@@ -228,7 +131,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             for (int g = 0; g < G; ++g)
                 if (g < subs) tma_gather4(a_base + g * SUB_A + (uint32_t)lane * 4u * RB, &tm, cc * TC_KCHUNK, idx[g], fb);
             if (lane < subs) {
-                const int k = (RB == 128 ? active[a] : active[it * G + lane]) + group;
+                const int k = (RB == 128 ? active[a] : active[it * G + lane]);
                 bulk_g2s(a_base + TC_A_BYTES + lane * sub_b, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
             }
             // advance this warp's cursor by P items and prefetch the next item's neighbour indices
@@ -246,7 +149,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             tc_fence_after();
         }
         const uint32_t lane_base = tmem_d + ((uint32_t)(warp * 32) << 16);
-        for (int c0 = 0; c0 < cout_here; c0 += 16) {
+        for (int c0 = 0; c0 < p.cout; c0 += 16) {
             uint32_t v[16];
             if (n_items > 0) tmem_ld16(lane_base + (uint32_t)c0, v);
             else {
@@ -257,10 +160,10 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                 float f[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < cout_here) ? __ldg(p.bias + col0 + c0 + j) : 0.f), p.act);
-                if ((cout_here & 15) == 0) {
+                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
+                if ((p.cout & 15) == 0) {
                     if (p.out_f32) {
-                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.out_ld + col0 + c0);
+                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
                     }
@@ -271,14 +174,14 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                             __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
                             pk[j] = *reinterpret_cast<uint32_t *>(&h);
                         }
-                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.out_ld + col0 + c0);
+                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
                         dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                         dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                     }
                 } else if (p.out_f32) {   // narrow heads (cout = 1, 3, ...): scalar stores of the real columns
 #pragma unroll
                     for (int j = 0; j < 16; ++j)
-                        if (c0 + j < cout_here) p.out_f32[o * p.out_ld + col0 + c0 + j] = f[j];
+                        if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
                 }
             }
         }
@@ -366,11 +269,7 @@ extern "C" int pcg_pack_weights_bf16(const float *weight, int K, int cin, int co
 }
 
 // ---------------------------------------------------------------------------- host side
-typedef CUresult (*PcgEncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static PcgEncodeTiled tensor_map_encoder() {
+PcgEncodeTiled pcg_tensor_map_encoder() {
     static PcgEncodeTiled fn = []() -> PcgEncodeTiled {
         void *p = nullptr;
         cudaDriverEntryPointQueryResult q;
@@ -383,16 +282,16 @@ static PcgEncodeTiled tensor_map_encoder() {
 extern "C" int pcg_tc_cin_padded(int cin) { return tc_cin_p(cin); }
 
 template <int RB>
-static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, int groups, cudaStream_t st) {
+static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cudaStream_t st) {
     PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_tc<RB><<<dim3((unsigned)cdiv(p.n_out, TC_ROWS), (unsigned)groups), 160, smem, st>>>(tm, p);
+    k_conv_tc<RB><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
     PCG_LAUNCHED();
     return 0;
 }
 
-static int conv_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                        const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
-                        int act, float *out_f32, void *out_bf16, long out_ld, int cout_total, int groups, void *stream) {
+extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                               int act, float *out_f32, void *out_bf16, void *stream) {
     PCG_CHECK_ARG(cin >= 1 && cin <= 1024, "pcg_conv_fwd_tc: cin=%d", cin);
     PCG_CHECK_ARG(cout >= 1 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be in [1,256]", cout);
     PCG_CHECK_ARG(out_bf16 == nullptr || (cout & 15) == 0, "pcg_conv_fwd_tc: a bf16 output needs cout %% 16 == 0 (cout=%d)", cout);
@@ -404,7 +303,7 @@ static int conv_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_
     PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)wpacked & 15) == 0, "pcg_conv_fwd_tc: operands must be 16-byte aligned");
     if (n_out <= 0) return 0;
     const int cin_p = tc_cin_p(cin), rb = tc_rb(cin_p);
-    PcgEncodeTiled encode = tensor_map_encoder();
+    PcgEncodeTiled encode = pcg_tensor_map_encoder();
     PCG_CHECK_ARG(encode != nullptr, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled is not available from this driver");
     CUtensorMap tm;
     {
@@ -424,7 +323,6 @@ static int conv_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_
     p.n_out = n_out; p.cout = cout; p.cout_p = tc_cout_p(cout); p.K = K;
     p.chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
     p.act = act;
-    p.out_ld = out_ld; p.cout_total = cout_total;
     p.tmem_cols = 32;
     while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
     const size_t stage_bytes = TC_A_BYTES + (size_t)p.cout_p * 128;
@@ -434,27 +332,7 @@ static int conv_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
     cudaStream_t st = as_stream(stream);
-    if (rb == 32) return launch_tc<32>(tm, p, smem, groups, st);
-    if (rb == 64) return launch_tc<64>(tm, p, smem, groups, st);
-    return launch_tc<128>(tm, p, smem, groups, st);
-}
-
-extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
-                               int act, float *out_f32, void *out_bf16, void *stream) {
-    return conv_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
-                        cout, cout, 1, stream);
-}
-
-// Dense product on the same kernel: out_bf16[n][0..n_cols) = feats[n][:] @ Wmat[:, 0..n_cols), n_cols a multiple of 16.
-// wpacked = pcg_pack_weights_bf16 of a (G, cin, 256) tensor holding Wmat's columns in groups of 256 (zero padded),
-// G = ceil(n_cols / 256).  CTA (tile, g) computes one 128 x 256 block.  nbr/tile_mask: the identity map over n rows
-// (nbr[0][i] = i, padding -1; tile_mask word 0 = 1).
-extern "C" int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const int32_t *nbr, long nbr_pitch,
-                                     const uint32_t *tile_mask, const void *wpacked, long n_cols, void *out_bf16, void *stream) {
-    PCG_CHECK_ARG(n_cols >= 16 && (n_cols & 15) == 0 && n_cols < (1L << 30), "pcg_gemm_bf16_grouped: n_cols=%ld must be a multiple of 16", n_cols);
-    const int groups = (int)cdiv(n_cols, 256);
-    PCG_CHECK_ARG(groups <= 65535, "pcg_gemm_bf16_grouped: too many column groups (%d)", groups);
-    return conv_tc_impl(feats_bf16, n, cin, nbr, nbr_pitch, tile_mask, 1, n, wpacked, nullptr, 256, PCG_ACT_NONE, nullptr, out_bf16,
-                        n_cols, (int)n_cols, groups, stream);
+    if (rb == 32) return launch_tc<32>(tm, p, smem, st);
+    if (rb == 64) return launch_tc<64>(tm, p, smem, st);
+    return launch_tc<128>(tm, p, smem, st);
 }

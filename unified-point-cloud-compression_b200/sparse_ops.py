@@ -107,7 +107,7 @@ class CoordSet:
             self._strided[stride] = hit
         return hit
 
-    def generated(self, ksize, stride):
+    def generated(self, ksize, stride, guess_per_row=40):
         """Coordinates of a generative transposed convolution (kernel ksize, up-sampling `stride`)."""
         key = (int(ksize), int(stride))
         hit = self._generated.get(key)
@@ -119,7 +119,7 @@ class CoordSet:
             lib = _lib.load()
             n_cand = self.n * K
             # exact for disjoint children (even kernel == stride); a surface estimate otherwise, retried on overflow
-            max_out = n_cand if (ksize == stride or self.n < 4096) else min(n_cand, 40 * self.n)
+            max_out = n_cand if (ksize == stride or self.n < 4096) else min(n_cand, guess_per_row * self.n)
             while True:
                 cap = lib.pcg_hash_capacity(max(max_out, 1))
                 keys = torch.empty(cap, dtype=torch.int64, device=dev)
@@ -141,6 +141,29 @@ class CoordSet:
             self._generated[key] = hit
         return hit
 
+    def generated_cells(self):
+        """Children of the kernel-5 / stride-2 generative up-sampling, organised by octree cells (pcg_cells.cu).
+        Same coordinate SET as generated(5, 2); rows are cell-major."""
+        hit = self._generated.get("cells")
+        if hit is None:
+            assert self.ts % 2 == 0, "fractional output tensor stride"
+            dev = self.coords.device
+            lib = _lib.load()
+            cells = self.generated(3, 1, guess_per_row=14)                # parents dilated by {-1,0,1}^3 * ts
+            pnbr, _ = self.kernel_map(cells, 3, False)                    # pnbr[e][cell] = parent row at cell + e*ts
+            mask = torch.empty(max(cells.n, 1), dtype=torch.uint8, device=dev)
+            base = torch.empty(max(cells.n, 1), dtype=torch.int32, device=dev)
+            cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+            ws = scratch(lib.pcg_cells_scratch_bytes(max(cells.n, 1)), dev)
+            call("pcg_cells_info", ptr(pnbr), pnbr.shape[1], cells.n, ptr(mask), ptr(base), ptr(cnt), ptr(ws), ws.numel(), stream())
+            n_out = int(cnt.item())
+            out = torch.empty((n_out, 4), dtype=torch.int32, device=dev)
+            out_cell = torch.empty(max(n_out, 1), dtype=torch.int32, device=dev)
+            call("pcg_cells_emit", ptr(cells.coords), ptr(mask), ptr(base), cells.n, self.ts // 2, ptr(out), ptr(out_cell), stream())
+            hit = CellCoordSet(out, self.ts // 2, self, cells, pnbr, mask, base, out_cell)
+            self._generated["cells"] = hit
+        return hit
+
     # -- kernel maps -------------------------------------------------------------------------
     def kernel_map(self, out_set, ksize, transposed):
         """nbr[K][pitch] (rows of THIS set feeding each output row; pitch = n_out rounded up to 128, padding -1)
@@ -159,6 +182,33 @@ class CoordSet:
             call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
                  int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), pitch, ptr(tmask), stream())
             hit = (nbr, tmask, None if out_set is self else out_set)   # keep out_set alive while cached (id() key)
+            self._kmaps[key] = hit
+        return hit[0], hit[1]
+
+
+class CellCoordSet(CoordSet):
+    """Candidate set of a kernel-5 / stride-2 generative up-sampling: children grouped by cell, with the cell table,
+    the per-cell parent lists and child masks that replace a hash table over the children (pcg.h, octree-cell section)."""
+
+    def __init__(self, coords, tensor_stride, parent, cells, pnbr, cell_mask, cell_base, out_cell):
+        super().__init__(coords, tensor_stride)
+        self.parent, self.cells, self.pnbr = parent, cells, pnbr
+        self.cell_mask, self.cell_base, self.out_cell = cell_mask, cell_base, out_cell
+
+    def kernel_map(self, out_set, ksize, transposed):
+        if out_set is not self or ksize != 3 or transposed:
+            return super().kernel_map(out_set, ksize, transposed)
+        key = (id(out_set), 3, False)
+        hit = self._kmaps.get(key)
+        if hit is None:
+            dev = self.coords.device
+            ckeys, cvals, ccap = self.cells.table()
+            pitch = _lib.load().pcg_nbr_pitch(self.n)
+            nbr = torch.empty((27, pitch), dtype=torch.int32, device=dev)
+            tmask = torch.empty((max((self.n + 127) // 128, 1), 4), dtype=torch.int32, device=dev)
+            call("pcg_cells_kernel_map3", ptr(ckeys), ptr(cvals), ccap, ptr(self.coords), ptr(self.out_cell), self.n, self.ts,
+                 ptr(self.cell_mask), ptr(self.cell_base), ptr(nbr), pitch, ptr(tmask), stream())
+            hit = (nbr, tmask, None)
             self._kmaps[key] = hit
         return hit[0], hit[1]
 
@@ -235,18 +285,21 @@ def to_bf16(feats):
 
 
 class PackedWeights:
-    """bf16 UMMA operand image of a (K,cin,cout) kernel, rebuilt when the parameter changes."""
+    """bf16 operand image of a (K,cin,cout) kernel, rebuilt when the parameter changes.
+    kind "umma": K-major swizzled tiles for tcgen05; kind "mma": mma.sync B fragments for the narrow-head kernel."""
 
     def __init__(self):
         self.key, self.buf = None, None
 
-    def get(self, w3):
-        key = (w3.data_ptr(), w3._version, tuple(w3.shape))
+    def get(self, w3, kind="umma"):
+        key = (w3.data_ptr(), w3._version, tuple(w3.shape), kind)
         if key != self.key:
             K, cin, cout = w3.shape
-            nbytes = _lib.load().pcg_packed_weight_bytes(K, cin, cout)
+            lib = _lib.load()
+            nbytes = lib.pcg_packed_weight_bytes(K, cin, cout) if kind == "umma" else lib.pcg_mma_weight_bytes(K, cin, cout)
             buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
-            call("pcg_pack_weights_bf16", ptr(w3.contiguous()), K, cin, cout, ptr(buf), stream())
+            call("pcg_pack_weights_bf16" if kind == "umma" else "pcg_pack_weights_mma", ptr(w3.contiguous()), K, cin, cout,
+                 ptr(buf), stream())
             self.key, self.buf = key, buf
         return self.buf
 
@@ -312,7 +365,7 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     if mode == "tc" and not use_tc:
         raise RuntimeError(f"conv shape K={K} cin={cin} cout={cout} is not tensor-core eligible")
     if not use_tc and feats.dtype == torch.bfloat16:
-        raise RuntimeError("bf16 features need the tensor-core path")
+        feats = feats[:, :cin].float()          # a bf16 hidden activation feeding a layer too small for the tensor-core paths
     prof = profiler
     if prof is not None:
         pairs = prof.pairs(nbr)
@@ -321,6 +374,30 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
             act_mean = float(sum(((tmask.view(-1).to(torch.int64) & 0xFFFFFFFF) >> i & 1).sum() for i in range(32)).item()) / max(tmask.shape[0], 1) if tmask is not None else float(K)
             prof.launches.append({"shape": (K, cin, cout), "n_in": int(feats.shape[0]), "n_out": int(n_out), "pairs": pairs,
                                   "active_per_tile": act_mean, "transposed": bool(transposed), "e": (e0, e1)})
+    # "tc" forces the tcgen05 kernel (tests pin its layouts on these shapes too); "auto" sends the narrow heads to the
+    # register-gather mma.sync kernel
+    narrow = use_tc and _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
+        _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+    if narrow:
+        fb = to_bf16(feats)
+        want_bf16 = out in ("bf16", "both")
+        want_f32 = out != "bf16"
+        of = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device) if want_f32 else None
+        ob = torch.empty((n_out, 16), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
+        if prof is not None:
+            e0.record()
+        wf = (packed or PackedWeights()).get(w3.detach(), kind="mma")
+        call("pcg_conv_fwd_mma", ptr(fb), feats.shape[0], cin, ptr(nbr), nbr.shape[1], K, n_out, ptr(wf), ptr(b), cout,
+             int(act), ptr(of), ptr(ob), stream())
+        if prof is not None:
+            e1.record()
+            prof.records.append(("conv_narrow", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                 2.0 * feats.shape[0] * cin_padded(cin) + (4.0 if want_f32 else 2.0) * n_out * cout + 4.0 * K * n_out, e0, e1))
+        if of is None:
+            return ob
+        if ob is not None:
+            of._pcg_bf16 = (ob, of._version)
+        return of
     if use_tc:
         fb = to_bf16(feats)
         wp = (packed or PackedWeights()).get(w3.detach())
@@ -351,6 +428,75 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
         e1.record()
         prof.records.append(("conv_f32", (K, cin, cout), 2.0 * pairs * cin * cout,
                              4.0 * f.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
+    return of
+
+
+class PackedGemmWeights:
+    """bf16 operand image of a (K,cin,cout) kernel seen as the dense matrix [cin x K*cout] in column groups of 256."""
+
+    def __init__(self):
+        self.key, self.buf = None, None
+
+    def get(self, w3):
+        key = (w3.data_ptr(), w3._version, tuple(w3.shape))
+        if key != self.key:
+            K, cin, cout = w3.shape
+            n_cols = K * cout
+            G = (n_cols + 255) // 256
+            wm = torch.zeros((cin, G * 256), dtype=torch.float32, device=w3.device)
+            wm[:, :n_cols] = w3.permute(1, 0, 2).reshape(cin, n_cols)
+            wg = wm.view(cin, G, 256).permute(1, 0, 2).contiguous()
+            nbytes = _lib.load().pcg_packed_weight_bytes(G, cin, 256)
+            buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
+            call("pcg_pack_weights_bf16", ptr(wg), G, cin, 256, ptr(buf), stream())
+            self.key, self.buf = key, buf
+        return self.buf
+
+
+def cells_eligible(ksize, stride, cin, cout):
+    """Static rule for the octree-cell / GEMM-first generative transposed convolution."""
+    return ksize == 5 and stride == 2 and cout in (32, 64, 128, 256) and 33 <= cin <= 128 and _conv_mode != "f32"
+
+
+def gen_conv_transpose_cells(feats, in_set, out_set, weight, bias, act=ACT_NONE, packed=None, out="f32"):
+    """Kernel-5 / stride-2 generative transposed convolution, GEMM-first: T[p][k] = F[p] @ W[k] as one dense
+    tcgen05 product over all parents (every (parent, offset) pair hits, so there is nothing to gather), then each
+    child sums the <= 27 rows of T its parents hold for it (pcg_cells_reduce, fixed order)."""
+    _need_cuda(feats, "features")
+    K, cin, cout = weight.shape
+    assert K == 125 and isinstance(out_set, CellCoordSet) and out_set.parent is in_set
+    dev = feats.device
+    n_par, n_out = in_set.n, out_set.n
+    want_bf16 = out in ("bf16", "both")
+    want_f32 = out != "bf16"
+    of = torch.empty((n_out, cout), dtype=torch.float32, device=dev) if want_f32 else None
+    ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=dev) if want_bf16 else None
+    if n_out == 0 or n_par == 0:
+        return of if of is not None else ob
+    fb = to_bf16(feats)
+    wp = (packed or PackedGemmWeights()).get(weight.detach())
+    n_cols = K * cout
+    T = torch.empty((n_par, n_cols), dtype=torch.bfloat16, device=dev)
+    prof = profiler
+    if prof is not None:
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+    call("pcg_gemm_bf16_grouped", ptr(fb), n_par, cin, ptr(wp), n_cols, ptr(T), stream())
+    if prof is not None:
+        e1.record()
+    b = bias.reshape(-1).contiguous() if bias is not None else None
+    call("pcg_cells_reduce", ptr(T), cout, ptr(out_set.pnbr), out_set.pnbr.shape[1], ptr(out_set.cell_mask), ptr(out_set.cell_base),
+         out_set.cells.n, ptr(b), int(act), ptr(of), ptr(ob), stream())
+    if prof is not None:
+        e2.record()
+        flops = 2.0 * n_par * K * cin * cout
+        prof.records.append(("conv_tc", (K, cin, cout), flops, 2.0 * n_par * cin + 2.0 * n_par * n_cols, e0, e1))
+        prof.records.append(("gent_reduce", (K, cin, cout), 0.0, 2.0 * n_par * n_cols + (2.0 if want_bf16 else 0) * n_out * cout
+                             + (4.0 if want_f32 else 0) * n_out * cout, e1, e2))
+    if of is None:
+        return ob
+    if ob is not None:
+        of._pcg_bf16 = (ob, of._version)
     return of
 
 
