@@ -89,7 +89,7 @@ def build_product_model(pkg, cfg, state_dict, device):
     return net
 
 
-def tiny_codec_roundtrip(pkg, device, width=32, seed=0, mode="auto"):
+def tiny_codec_roundtrip(pkg, device, width=32, seed=0, mode="auto", return_clouds=False):
     """Encode + decode a small sphere on the GPU and check it against oracle/pipeline_ref.py on the same
     weights: stride-8 coordinates and k bit-exact, symbols near-exact, decoded geometry/colours close.
 
@@ -136,4 +136,7 @@ def tiny_codec_roundtrip(pkg, device, width=32, seed=0, mode="auto"):
     need = 0.99 if mode == "f32" else 0.25
     assert len(ia) >= need * len(rrec), f"decoded geometry overlap {len(ia)}/{len(rrec)}"
     assert np.abs(rec[ia, 3:] - rrec[ib, 3:]).mean() < 0.02
-    return {"n": len(pts), "overlap": len(ia) / len(rrec), "symbol_mismatch": frac}
+    stats = {"n": len(pts), "overlap": len(ia) / len(rrec), "symbol_mismatch": frac}
+    if return_clouds:
+        stats.update(source=np.concatenate([pts.astype(np.float64), rgb], axis=1), rec=rec.astype(np.float64), ref_rec=np.asarray(rrec, np.float64))
+    return stats

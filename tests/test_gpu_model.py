@@ -127,3 +127,18 @@ def test_encoder_decoder_agree_on_indexes_bitwise(pkg, dev):
             return enc["y_symbols"]
         net.decode_block(enc["y_points"], enc["z_symbols"], grab, enc["k"], q)
     assert torch.equal(seen["idx"].reshape(-1), enc["y_indexes"].reshape(-1))
+
+
+@pytest.mark.parametrize("mode", ["f32", "auto"])
+def test_decoded_psnr_matches_oracle(pkg, dev, mode):
+    """The north-star's quality gate: D1-PSNR and Y-PSNR of the decoded cloud (metrics/metric.py restated in
+    oracle/metric_ref.py) within 0.05 dB of the CPU oracle's decode of the same input with the same weights."""
+    from oracle import metric_ref
+    stats = tiny_codec_roundtrip(pkg, dev, width=32, mode=mode, return_clouds=True)
+    src, rec, rrec = stats["source"], stats["rec"], stats["ref_rec"]
+    got = metric_ref.pointcloud_metrics(src, rec, resolution=63)
+    ref = metric_ref.pointcloud_metrics(src, rrec, resolution=63)
+    d1 = abs(got["sym_psnr_mse"] - ref["sym_psnr_mse"])
+    y = abs(got["sym_y_psnr"] - ref["sym_y_psnr"])
+    print(f"[psnr {mode}] D1 {got['sym_psnr_mse']:.3f} vs {ref['sym_psnr_mse']:.3f} dB, Y {got['sym_y_psnr']:.3f} vs {ref['sym_y_psnr']:.3f} dB")
+    assert d1 <= 0.05 and y <= 0.05, f"D1-PSNR delta {d1:.3f} dB, Y-PSNR delta {y:.3f} dB"

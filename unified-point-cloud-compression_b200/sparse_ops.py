@@ -490,7 +490,7 @@ def gen_conv_transpose_cells(feats, in_set, out_set, weight, bias, act=ACT_NONE,
     if prof is not None:
         e2.record()
         flops = 2.0 * n_par * K * cin * cout
-        prof.records.append(("conv_tc", (K, cin, cout), flops, 2.0 * n_par * cin + 2.0 * n_par * n_cols, e0, e1))
+        prof.records.append(("gemm_first", (K, cin, cout), flops, 2.0 * n_par * cin + 2.0 * n_par * n_cols, e0, e1))
         prof.records.append(("gent_reduce", (K, cin, cout), 0.0, 2.0 * n_par * n_cols + (2.0 if want_bf16 else 0) * n_out * cout
                              + (4.0 if want_f32 else 0) * n_out * cout, e1, e2))
     if of is None:
