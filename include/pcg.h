@@ -103,6 +103,12 @@ size_t pcg_sort_rows_scratch_bytes(long n);
 int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr, long nbr_pitch, int K, long n_out,
                      const float *weight, const float *bias, int cout, int act, float *out, void *stream);
 
+/* Weight gradient dW[k] = sum_o F[nbr[k][o]]^T (x) G[o] (ME ConvolutionBackwardGPU; train.py:195-234), fp32, fixed
+ * summation order.  tile_mask (optional, K <= 128) skips empty (tile, offset) combinations.  The input gradient is the
+ * forward convolution of G over the inverse kernel map with W[k]^T and needs no entry point of its own. */
+int pcg_conv_bwd_weight_f32(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
+                            int K, long n_out, const float *gout, int cout, float *dweight, void *stream);
+
 /* bf16 tensor-core path (tcgen05.mma, fp32 accumulation in TMEM, operands gathered by TMA tile::gather4).
  * 1 <= cout <= 256, K <= 128, any cin >= 1, n_in >= 1.  feats_bf16: n_in rows of pcg_tc_cin_padded(cin) bf16
  * (16, 32 or a multiple of 64 channels, zero padded; pcg_f32_to_bf16_rows makes them); wpacked from

@@ -198,3 +198,39 @@ def test_gen_conv_transpose_cells_matches_oracle(pkg, dev, cin, cout, kind):
     again = so.gen_conv_transpose_cells(torch.from_numpy(Fm).to(dev), cs, out_set, torch.from_numpy(W).to(dev),
                                         torch.from_numpy(b).to(dev), act=so.ACT_RELU, out="f32")
     assert torch.equal(out, again)
+
+
+@pytest.mark.parametrize("cin,cout,ksize,stride,transposed", [(8, 16, 3, 1, False), (16, 8, 5, 2, False), (8, 8, 2, 2, True),
+                                                              (16, 16, 5, 2, True), (4, 24, 3, 2, False)])
+def test_conv_gradients_match_oracle_autograd(pkg, dev, cin, cout, ksize, stride, transposed):
+    """Training path: d(input), d(weight), d(bias) of the CUDA sparse convolution (fp32 mode) vs torch autograd through the
+    CPU oracle's convolution on the same kernel map."""
+    import importlib
+    so = pkg.sparse_ops
+    ag = importlib.import_module(pkg.__name__ + ".autograd")
+    ts = 2 if transposed else 1
+    C, cs = setup(dev, pkg, seed=3 * cin + cout, ts=ts)
+    out_set = cs.generated(ksize, stride) if transposed else cs.strided(stride)
+    C_out = out_set.coords.cpu().numpy()
+    rng = np.random.default_rng(cin + cout)
+    K = ksize ** 3
+    Fm = torch.from_numpy(rng.standard_normal((len(C), cin)).astype(np.float32))
+    W = torch.from_numpy((rng.standard_normal((K, cin, cout)) / np.sqrt(cin * K) * 3).astype(np.float32))
+    b = torch.from_numpy(rng.standard_normal((1, cout)).astype(np.float32))
+    G = torch.from_numpy(rng.standard_normal((len(C_out), cout)).astype(np.float32))
+    # oracle: plain torch ops over the oracle's kernel map
+    maps = me_ref.kernel_map(C, C_out, ksize, (ts // stride) if transposed else ts, transposed)
+    Fr, Wr, br = Fm.clone().requires_grad_(True), W.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = torch.relu(me_ref.sparse_conv_features(Fr, maps, Wr, br, len(C_out)))
+    (ref * G).sum().backward()
+    prev = so.set_conv_mode("f32")
+    try:
+        Fd, Wd, bd = (t.clone().to(dev).requires_grad_(True) for t in (Fm, W, b))
+        out = ag.sparse_conv_autograd(Fd, cs, out_set, Wd, bd, ksize, transposed, so.ACT_RELU)
+        (out * G.to(dev)).sum().backward()
+    finally:
+        so.set_conv_mode(prev)
+    assert rel_l2(out.detach().cpu().numpy(), ref.detach().numpy()) < 2e-5
+    for name, got, want in (("d_input", Fd.grad, Fr.grad), ("d_weight", Wd.grad, Wr.grad), ("d_bias", bd.grad, br.grad)):
+        err = rel_l2(got.cpu().numpy(), want.numpy())
+        assert err < 5e-5, f"{name}: rel-L2 {err:.3e}"

@@ -142,3 +142,36 @@ def test_decoded_psnr_matches_oracle(pkg, dev, mode):
     y = abs(got["sym_y_psnr"] - ref["sym_y_psnr"])
     print(f"[psnr {mode}] D1 {got['sym_psnr_mse']:.3f} vs {ref['sym_psnr_mse']:.3f} dB, Y {got['sym_y_psnr']:.3f} vs {ref['sym_y_psnr']:.3f} dB")
     assert d1 <= 0.05 and y <= 0.05, f"D1-PSNR delta {d1:.3f} dB, Y-PSNR delta {y:.3f} dB"
+
+
+@pytest.mark.parametrize("shepard", [False, True])
+def test_training_step_runs_and_learns(pkg, dev, shepard):
+    """BASELINE config 4 / 5 in miniature: forward (train mode) + focal / colour (or Shepard) / bpp losses + backward through
+    the CUDA convolutions + both Adam steps (train.py:195-234).  Every parameter that the loss depends on gets a finite
+    gradient and a few steps on one batch reduce the loss."""
+    import importlib
+    from oracle import synth
+    from tests.helpers import model_config
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    training = importlib.import_module(pkg.__name__ + ".training")
+    loss_mod = importlib.import_module(pkg.__name__ + ".model.loss")
+    torch.manual_seed(0)
+    net = model_mod.UnifiedModel(model_config(width=16)).to(dev)
+    clouds = [synth.small_cloud(seed=s, radius=9.0, centre=(16, 16, 16), n_samples=5000) for s in (1, 2)]
+    coords = torch.cat([torch.cat([torch.full((len(p), 1), b, dtype=torch.int32), torch.from_numpy(p)], 1) for b, (p, _) in enumerate(clouds)]).to(dev)
+    feats = torch.cat([torch.from_numpy(c.astype(np.float32)) for _, c in clouds]).to(dev)
+    q = torch.tensor([[0.5, 0.5], [0.2, 0.8]], device=dev)
+    prev = pkg.sparse_ops.set_conv_mode("f32")
+    try:
+        tr = training.Trainer(net, loss_mod.default_loss_config(shepard=shepard), model_lr=1e-3)
+        losses = []
+        for _ in range(6):
+            loss, aux, parts = tr.step(coords, feats, q)
+            assert torch.isfinite(loss) and torch.isfinite(aux)
+            losses.append(float(loss))
+    finally:
+        pkg.sparse_ops.set_conv_mode(prev)
+    missing = [n for n, p in net.named_parameters() if p.grad is None and not n.startswith(("g_s.down_conv", "entropy_model.rescale_nn"))]   # unused on this config (inverse_rescaling)
+    assert not missing, f"parameters without gradient: {missing}"
+    assert all(torch.isfinite(p.grad).all() for p in net.parameters() if p.grad is not None)
+    assert min(losses[1:]) < losses[0], losses      # (the colour term is defined on a changing voxel set, so not monotone)

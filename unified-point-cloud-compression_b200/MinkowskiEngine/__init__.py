@@ -101,6 +101,9 @@ class SparseTensor:
 
     def features_at_coordinates(self, query_coordinates):
         """ME6: trilinear interpolation at tensor-stride spacing; on-grid queries are exact row lookups."""
+        if torch.is_grad_enabled() and self._F.requires_grad:
+            from ..autograd import features_at_autograd
+            return features_at_autograd(self._F, self._cs, query_coordinates.to(self._F.device))
         return so.features_at(self._F, self._cs, query_coordinates)
 
     def _like(self, features, coord_set=None):
@@ -234,7 +237,11 @@ class MinkowskiPruning(nn.Module):
     def forward(self, input, mask):
         if mask.shape[0] != input.F.shape[0]:
             raise ValueError("mask and input must have the same number of rows")
-        oc, of = so.prune_rows(input.C, input.F, mask.to(input.device))
+        mask = mask.to(input.device)
+        if torch.is_grad_enabled() and input.F.requires_grad:
+            oc, _ = so.prune_rows(input.C, None, mask)
+            return SparseTensor(input.F[mask.bool()], _coord_set=so.CoordSet(oc, input.coord_set.ts))   # differentiable row gather
+        oc, of = so.prune_rows(input.C, input.F, mask)
         return SparseTensor(of, _coord_set=so.CoordSet(oc, input.coord_set.ts))
 
 
@@ -243,6 +250,8 @@ class MinkowskiReLU(nn.Module):
         super().__init__()
 
     def forward(self, input):
+        if torch.is_grad_enabled() and input.F.requires_grad:
+            return input._like(torch.relu(input.F))
         return input._like(so.activation(input.F, so.ACT_RELU))
 
 
@@ -254,6 +263,8 @@ class MinkowskiLeakyReLU(nn.Module):
         self.negative_slope = negative_slope
 
     def forward(self, input):
+        if torch.is_grad_enabled() and input.F.requires_grad:
+            return input._like(torch.nn.functional.leaky_relu(input.F, 0.01))
         return input._like(so.activation(input.F, so.ACT_LEAKY))
 
 

@@ -98,7 +98,11 @@ class SparseSynthesisTransform(nn.Module):
         """Rows under `mask`.  reorder=True additionally puts the survivors in Z-order (row order is free in ME
         semantics): they are the parents of the next generative level, whose candidates inherit the parents'
         order class by class -- without it spatial coherence (= L2 hit rate of every gather) decays level by level."""
-        oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
+        if torch.is_grad_enabled() and x.F.requires_grad:
+            oc, _ = so.prune_rows(x.C, None, mask, n_keep=n_keep)
+            of = x.F[mask]                              # differentiable row gather (training)
+        else:
+            oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
         if reorder and oc.shape[0] > 1 and not os.environ.get("PCG_NO_REORDER"):
             perm = so.sort_rows(oc, morton=True)
             oc, of = oc[perm].contiguous(), of[perm].contiguous()
