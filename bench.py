@@ -189,16 +189,29 @@ def main():
 
     bytes_io = {"h2d": 0, "d2h": 0}
 
+    pinned = {}
+
+    def to_host(name, t):
+        """D2H into a persistent pinned buffer (allocated on first use), asynchronous on the current stream."""
+        t = t.contiguous()
+        buf = pinned.get(name)
+        if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+            buf = pinned[name] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        buf.copy_(t, non_blocking=True)
+        return buf
+
     def step_e2e():
         x = host_cloud.to(dev, non_blocking=True)
         enc = net.encode_block(x, q)
-        host = {k: enc[k].contiguous().to("cpu", non_blocking=False) for k in ("y_points", "z_symbols", "y_symbols", "y_indexes")}
+        host = {k: to_host(k, enc[k]) for k in ("y_points", "z_symbols", "y_symbols", "y_indexes")}
+        torch.cuda.current_stream().synchronize()
         # (host range coder runs here in a deployment; excluded by the metric)
-        yp, zs, ys = (host[k].pin_memory().to(dev, non_blocking=True) for k in ("y_points", "z_symbols", "y_symbols"))
+        yp, zs, ys = (host[k].to(dev, non_blocking=True) for k in ("y_points", "z_symbols", "y_symbols"))
         x_hat = net.decode_block(yp, zs, lambda idx: ys, enc["k"], q)
-        rec = net.finalize(x_hat.C, x_hat.F).to("cpu")
-        bytes_io["h2d"] = x.numel() * 4 + sum(host[k].numel() * 4 for k in ("y_points", "z_symbols", "y_symbols"))
-        bytes_io["d2h"] = sum(v.numel() * 4 for v in host.values()) + rec.numel() * 4
+        rec = to_host("rec", net.finalize(x_hat.C, x_hat.F))
+        torch.cuda.current_stream().synchronize()
+        bytes_io["h2d"] = x.numel() * 4 + sum(host[k].numel() * host[k].element_size() for k in ("y_points", "z_symbols", "y_symbols"))
+        bytes_io["d2h"] = sum(v.numel() * v.element_size() for v in host.values()) + rec.numel() * rec.element_size()
         return rec
 
     def barrier():

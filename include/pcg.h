@@ -97,6 +97,10 @@ int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t *perm, void
                   void *stream);
 size_t pcg_sort_rows_scratch_bytes(long n);
 
+/* Block entry (model/model.py:142-161): (n,6) float rows [x y z r g b] -> coords[i] = (batch, floor(xyz[perm[i]])),
+ * feats[i] = (1, rgb[perm[i]]); perm may be NULL (identity). */
+int pcg_gather_block(const float *cloud, const int32_t *perm, long n, int batch, int32_t *coords, float *feats, void *stream);
+
 /* ---- sparse convolution: replaces ME ConvolutionForwardGPU / ConvolutionTransposeForwardGPU
  * (ME2-ME4).  out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]); accumulation order is fixed
  * (offset index ascending, then input channel), so results are bit-reproducible run to run. */

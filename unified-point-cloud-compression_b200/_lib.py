@@ -31,6 +31,7 @@ _PROTOS = {
     "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _L, _P, _P]),
     "pcg_sort_rows": (_I, [_P, _L, _I, _P, _P, _SZ, _P]),
     "pcg_sort_rows_scratch_bytes": (_SZ, [_L]),
+    "pcg_gather_block": (_I, [_P, _P, _L, _I, _P, _P, _P]),
     "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P]),
     "pcg_conv_bwd_weight_f32": (_I, [_P, _I, _P, _L, _P, _I, _L, _P, _I, _P, _P]),
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),

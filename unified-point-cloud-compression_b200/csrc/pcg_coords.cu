@@ -491,3 +491,26 @@ extern "C" int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t 
     pcg_launches.fetch_add(1, std::memory_order_relaxed);
     return 0;
 }
+
+// ---------------------------------------------------------------------------- block entry
+// One pass from the caller's (n,6) float rows [x y z r g b] to the codec's input tensor in a given row order:
+// coords[i] = (batch, floor(xyz[perm[i]])), feats[i] = (1, rgb[perm[i]])  (model/model.py:142-161: occupancy channel +
+// colours, integer coordinates).  Replaces four framework gathers / casts / concatenations.
+__global__ void k_gather_block(const float *__restrict__ cloud, const int32_t *__restrict__ perm, long n, int batch,
+                               int32_t *__restrict__ coords, float *__restrict__ feats) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *src = cloud + (long)(perm ? perm[i] : i) * 6;
+    const float2 a = __ldg(reinterpret_cast<const float2 *>(src)), b = __ldg(reinterpret_cast<const float2 *>(src) + 1),
+                 c = __ldg(reinterpret_cast<const float2 *>(src) + 2);
+    reinterpret_cast<int4 *>(coords)[i] = make_int4(batch, (int)floorf(a.x), (int)floorf(a.y), (int)floorf(b.x));
+    reinterpret_cast<float4 *>(feats)[i] = make_float4(1.f, b.y, c.x, c.y);
+}
+
+extern "C" int pcg_gather_block(const float *cloud, const int32_t *perm, long n, int batch, int32_t *coords, float *feats, void *stream) {
+    PCG_CHECK_ARG(((uintptr_t)cloud & 7) == 0 && ((uintptr_t)coords & 15) == 0 && ((uintptr_t)feats & 15) == 0, "pcg_gather_block: misaligned buffers");
+    if (n <= 0) return 0;
+    k_gather_block<<<(unsigned)cdiv(n, 256), 256, 0, as_stream(stream)>>>(cloud, perm, n, batch, coords, feats);
+    PCG_LAUNCHED();
+    return 0;
+}

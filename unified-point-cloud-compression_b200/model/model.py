@@ -59,16 +59,15 @@ class UnifiedModel(CompressionModel):
         Rows are put in Z-order first: MinkowskiEngine semantics do not depend on row order, and every derived
         coordinate set (strided / generated, first-occurrence order) inherits the spatial coherence, which is what
         lets a 128-row convolution tile skip the kernel offsets its surface patch does not use."""
-        dev = x_block.device
-        coords4 = torch.cat([torch.zeros((x_block.shape[0], 1), dtype=torch.int32, device=dev),
-                             torch.floor(x_block[:, :3]).to(torch.int32)], dim=1)
-        order = so.sort_rows(coords4, morton=True)
-        coords4, rgb = coords4[order].contiguous(), x_block[order, 3:6]
+        coords0, _ = so.gather_block(x_block)                      # integer coordinates, caller's row order (sort keys only)
+        order = so.sort_rows_i32(coords0, morton=True)
+        coords4, feats = so.gather_block(x_block, order)           # one pass: Z-ordered coordinates + [1, r, g, b] rows
         uniq, index, table = so.unique_first(coords4)
         if uniq.shape[0] != coords4.shape[0]:
-            coords4, rgb = uniq, rgb[index.long()]
-        feats = torch.cat([torch.ones((coords4.shape[0], 1), device=dev), rgb], dim=1)
-        return ME.SparseTensor(feats, _coord_set=so.CoordSet(coords4, 1, table=table))
+            coords4, feats = uniq, feats[index.long()]
+        cs = so.CoordSet(coords4, 1, table=table)
+        cs.single_batch = True                                     # one block = one batch item: level sizes are row counts
+        return ME.SparseTensor(feats, _coord_set=cs)
 
     def encode_block(self, x_block, q):
         """g_a + hyper-analysis + quantisation + CDF indexes on the GPU; returns device symbol buffers + k."""

@@ -50,7 +50,10 @@ class AnalysisTransform(nn.Module):
     count_per_batch = staticmethod(count_per_batch)
 
     def forward(self, x):
-        k = [count_per_batch(x)]
+        if getattr(x.coord_set, "single_batch", False):
+            k = [[x.F.shape[0]]]                     # known single batch item (block entry): no bincount / sync
+        else:
+            k = [count_per_batch(x)]
         single = len(k[0]) == 1                      # one batch item: level sizes are just row counts
         x = self.down_conv_1(x)
         k.append([x.F.shape[0]] if single else count_per_batch(x))

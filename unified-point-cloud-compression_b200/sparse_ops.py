@@ -192,8 +192,11 @@ class CellCoordSet(CoordSet):
 
     def __init__(self, coords, tensor_stride, parent, cells, pnbr, cell_mask, cell_base, out_cell):
         super().__init__(coords, tensor_stride)
-        self.parent, self.cells, self.pnbr = parent, cells, pnbr
+        self._parent = weakref.ref(parent)      # weak: the parent caches this set (no reference cycle -> memory is freed by refcount)
+        self.cells, self.pnbr = cells, pnbr
         self.cell_mask, self.cell_base, self.out_cell = cell_mask, cell_base, out_cell
+
+    parent = property(lambda self: self._parent())
 
     def kernel_map(self, out_set, ksize, transposed):
         if out_set is not self or ksize != 3 or transposed:
@@ -244,8 +247,8 @@ def unique_first(coords):
     return out[:m], index[:m], (keys, vals, cap)
 
 
-def sort_rows(coords, morton=False):
-    """Row permutation: lexicographic (b,x,y,z) (utils.py:142-187) or, with morton=True, (b, Z-order)."""
+def sort_rows_i32(coords, morton=False):
+    """Row permutation (int32): lexicographic (b,x,y,z) (utils.py:142-187) or, with morton=True, (b, Z-order)."""
     _need_cuda(coords, "coordinates")
     coords = coords.to(torch.int32).contiguous()
     n = coords.shape[0]
@@ -254,7 +257,22 @@ def sort_rows(coords, morton=False):
         lib = _lib.load()
         ws = scratch(lib.pcg_sort_rows_scratch_bytes(n), coords.device)
         call("pcg_sort_rows", ptr(coords), n, int(bool(morton)), ptr(perm), ptr(ws), ws.numel(), stream())
-    return perm.long()
+    return perm
+
+
+def sort_rows(coords, morton=False):
+    return sort_rows_i32(coords, morton).long()
+
+
+def gather_block(cloud, perm=None, batch=0):
+    """(n,6) float rows [xyz|rgb] -> (coords (n,4) int32 = (batch, floor xyz), feats (n,4) = (1, rgb)), rows taken in `perm` order."""
+    _need_cuda(cloud, "point cloud")
+    c = cloud.to(torch.float32).contiguous()
+    n = c.shape[0]
+    coords = torch.empty((n, 4), dtype=torch.int32, device=c.device)
+    feats = torch.empty((n, 4), dtype=torch.float32, device=c.device)
+    call("pcg_gather_block", ptr(c), ptr(perm), n, int(batch), ptr(coords), ptr(feats), stream())
+    return coords, feats
 
 
 def lexsort(coords):
