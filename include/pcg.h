@@ -129,6 +129,12 @@ int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
 /* n rows of c floats -> n rows of c_padded >= c bf16, zero padded. */
 int pcg_f32_to_bf16_rows(const float *src, long n, int c, int c_padded, void *dst, void *stream);
 
+/* im2col for layers with a tiny C_in (the 4-channel input layer, model/transforms.py:33): col[o][k*cin + c] =
+ * F[nbr[k][o]][c] as bf16, zeros where absent, row_elems (a multiple of cin, >= K*cin) elements per row.  The layer
+ * is then the dense product col @ W.reshape(K*cin, cout): pcg_conv_fwd_tc with K = 1 and the identity map. */
+int pcg_im2col_bf16(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, int K, long n_out, int row_elems,
+                    void *col_bf16, void *stream);
+
 /* Narrow occupancy-head layers on bf16 rows gathered by 8/16-byte loads straight into mma.sync A fragments
  * (csrc/pcg_conv_narrow.cu; model/transforms.py:146-160).  Same arithmetic contract as pcg_conv_fwd_tc (bf16 operands,
  * fp32 accumulation, fixed order).  C_in <= 64 (rows of pcg_tc_cin_padded(cin) bf16), C_out <= 16; wfrag from

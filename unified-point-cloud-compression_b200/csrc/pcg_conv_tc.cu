@@ -16,13 +16,15 @@
 // offsets.  Kernel offsets no row of the tile uses are skipped (tile_mask from pcg_kernel_map).  Every output element
 // is one fixed-order chain of MMAs over ascending (k, cin-chunk): bit-reproducible, and independent of which
 // tile a row lands in (absent neighbours contribute exact zeros).
+#include <stdlib.h>
+
 #include "pcg_tc.cuh"
 
 #define TC_ROWS 128
 #define TC_KCHUNK 64                       // bf16 elements per 128-byte swizzled row
 #define TC_A_BYTES (TC_ROWS * 128)         // 16 KiB per stage
 #define TC_LAG 2                           // cp.async groups in flight per producer thread
-#define TC_MAX_STAGES 6
+#define TC_MAX_STAGES 12
 
 struct TcParams {
     const int32_t *nbr;           // [K][nbr_pitch], padding entries -1
@@ -326,8 +328,11 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.tmem_cols = 32;
     while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
     const size_t stage_bytes = TC_A_BYTES + (size_t)p.cout_p * 128;
-    int stages = (int)((108 * 1024) / stage_bytes);   // two CTAs per SM where the tile allows it
+    static const int budget_kb = getenv("PCG_TC_SMEM_KB") ? atoi(getenv("PCG_TC_SMEM_KB")) : 108;   // tuning knob (tools/bench_conv.py)
+    static const int max_stages = getenv("PCG_TC_STAGES") ? atoi(getenv("PCG_TC_STAGES")) : TC_MAX_STAGES;
+    int stages = (int)(((size_t)budget_kb * 1024) / stage_bytes);   // default: two CTAs per SM where the tile allows it
     if (stages < 3) stages = 3;
+    if (stages > max_stages) stages = max_stages;
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;

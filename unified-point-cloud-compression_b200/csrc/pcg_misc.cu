@@ -287,3 +287,50 @@ extern "C" int pcg_features_at(const uint64_t *keys, const int32_t *vals, long c
     PCG_LAUNCHED();
     return 0;
 }
+
+// ---------------------------------------------------------------------------- im2col for tiny C_in
+// The first analysis layer has C_in = 4 and 125 offsets: gathered row by row it costs 125 row requests of 8 useful bytes
+// per output.  Instead, lay the whole receptive field of an output row out as ONE dense bf16 row
+// col[o][k*cin + c] = F[nbr[k][o]][c] (zeros where absent, zero padded to a multiple of 64), after which the layer is a
+// plain dense product col @ W.reshape(K*cin, cout) on the tensor-core kernel with the identity map.
+// One thread = one output row x 4 consecutive offsets (a full 32-byte sector of the col row for cin = 4).
+template <int CIN>
+__global__ void k_im2col_bf16(const float *__restrict__ feats, const int32_t *__restrict__ nbr, long pitch, int K, long n_out,
+                              int row_elems, __nv_bfloat16 *__restrict__ col) {
+    const int kgroups = row_elems / (4 * CIN);             // groups of 4 offsets, including the zero padding
+    long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    long o = t % n_out;                                    // consecutive threads -> consecutive rows: coalesced nbr reads
+    int kg = (int)(t / n_out);
+    if (kg >= kgroups) return;
+    __align__(16) __nv_bfloat16 v[4 * CIN];
+    int idx[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) idx[j] = (kg * 4 + j < K) ? __ldg(nbr + (long)(kg * 4 + j) * pitch + o) : -1;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < CIN; ++c) v[j * CIN + c] = __float2bfloat16_rn(idx[j] >= 0 ? __ldg(feats + (long)idx[j] * CIN + c) : 0.f);
+    uint2 *dst = reinterpret_cast<uint2 *>(col + o * row_elems + (long)kg * 4 * CIN);
+    const uint2 *src = reinterpret_cast<const uint2 *>(v);
+#pragma unroll
+    for (int q = 0; q < CIN; ++q) dst[q] = src[q];         // 8*CIN bytes per thread (one 32-byte sector for CIN = 4)
+}
+
+extern "C" int pcg_im2col_bf16(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, int K, long n_out, int row_elems,
+                               void *col_bf16, void *stream) {
+    PCG_CHECK_ARG((cin == 1 || cin == 2 || cin == 4 || cin == 8) && K >= 1 && row_elems >= K * cin && row_elems % (4 * cin) == 0,
+                  "pcg_im2col_bf16: cin=%d (1, 2, 4 or 8) K=%d row_elems=%d (a multiple of 4*cin, >= K*cin)", cin, K, row_elems);
+    if (n_out <= 0) return 0;
+    const long kgroups = row_elems / (4 * cin);
+    const unsigned blocks = (unsigned)cdiv(n_out * kgroups, 256);
+    __nv_bfloat16 *col = reinterpret_cast<__nv_bfloat16 *>(col_bf16);
+    cudaStream_t st = as_stream(stream);
+    switch (cin) {
+        case 1: k_im2col_bf16<1><<<blocks, 256, 0, st>>>(feats, nbr, nbr_pitch, K, n_out, row_elems, col); break;
+        case 2: k_im2col_bf16<2><<<blocks, 256, 0, st>>>(feats, nbr, nbr_pitch, K, n_out, row_elems, col); break;
+        case 4: k_im2col_bf16<4><<<blocks, 256, 0, st>>>(feats, nbr, nbr_pitch, K, n_out, row_elems, col); break;
+        default: k_im2col_bf16<8><<<blocks, 256, 0, st>>>(feats, nbr, nbr_pitch, K, n_out, row_elems, col); break;
+    }
+    PCG_LAUNCHED();
+    return 0;
+}

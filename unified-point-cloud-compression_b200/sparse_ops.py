@@ -164,6 +164,20 @@ class CoordSet:
             self._generated["cells"] = hit
         return hit
 
+    def identity_map(self):
+        """nbr / tile_mask of the identity (row i <- row i): operand map of a dense product on the sparse-conv kernel."""
+        hit = self._kmaps.get("identity")
+        if hit is None:
+            dev = self.coords.device
+            pitch = _lib.load().pcg_nbr_pitch(self.n)
+            nbr = torch.arange(pitch, dtype=torch.int32, device=dev)
+            nbr[self.n:] = -1
+            tmask = torch.zeros((max((self.n + 127) // 128, 1), 4), dtype=torch.int32, device=dev)
+            tmask[:, 0] = 1
+            hit = (nbr.view(1, pitch), tmask)
+            self._kmaps["identity"] = hit
+        return hit
+
     # -- kernel maps -------------------------------------------------------------------------
     def kernel_map(self, out_set, ksize, transposed):
         """nbr[K][pitch] (rows of THIS set feeding each output row; pitch = n_out rounded up to 128, padding -1)
@@ -314,6 +328,11 @@ class PackedWeights:
         if key != self.key:
             K, cin, cout = w3.shape
             lib = _lib.load()
+            if kind == "im2col":        # (K,cin,cout) seen as one dense (1, roundup64(K*cin), cout) kernel
+                rows = im2col_row_elems(K, cin)
+                w2 = torch.zeros((1, rows, cout), dtype=torch.float32, device=w3.device)
+                w2[0, :K * cin] = w3.reshape(K * cin, cout)
+                w3, K, cin, kind = w2, 1, rows, "umma"
             nbytes = lib.pcg_packed_weight_bytes(K, cin, cout) if kind == "umma" else lib.pcg_mma_weight_bytes(K, cin, cout)
             buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
             call("pcg_pack_weights_bf16" if kind == "umma" else "pcg_pack_weights_mma", ptr(w3.contiguous()), K, cin, cout,
@@ -351,6 +370,15 @@ class ConvProfiler:
 
 
 profiler = None      # set to a ConvProfiler() to time every convolution launch
+
+
+def im2col_row_elems(K, cin):
+    return (K * cin + 63) // 64 * 64
+
+
+def im2col_eligible(K, cin, cout):
+    """Tiny C_in with many offsets (the 4-channel input layer): dense col @ W instead of K row gathers per output."""
+    return cin in (1, 2, 4, 8) and K >= 27 and im2col_row_elems(K, cin) <= 1024 and 16 <= cout <= 256
 
 
 def tc_eligible(K, cin, cout):
@@ -396,6 +424,29 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     # register-gather mma.sync kernel
     narrow = use_tc and _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
         _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+    if use_tc and _conv_mode == "auto" and feats.dtype == torch.float32 and im2col_eligible(K, cin, cout):
+        rows = im2col_row_elems(K, cin)
+        col = torch.empty((n_out, rows), dtype=torch.bfloat16, device=feats.device)
+        want_bf16 = out in ("bf16", "both") and cout == cin_padded(cout)
+        want_f32 = out != "bf16" or not want_bf16
+        of = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device) if want_f32 else None
+        ob = torch.empty((n_out, cout), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
+        wp = (packed or PackedWeights()).get(w3.detach(), kind="im2col")
+        inbr, itm = out_set.identity_map()
+        if prof is not None:
+            e0.record()
+        call("pcg_im2col_bf16", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], K, n_out, rows, ptr(col), stream())
+        call("pcg_conv_fwd_tc", ptr(col), n_out, rows, ptr(inbr), inbr.shape[1], ptr(itm), 1, n_out, ptr(wp), ptr(b), cout,
+             int(act), ptr(of), ptr(ob), stream())
+        if prof is not None:
+            e1.record()
+            prof.records.append(("conv_tc", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                 4.0 * feats.shape[0] * cin + (4.0 if want_f32 else 2.0) * n_out * cout, e0, e1))
+        if of is None:
+            return ob
+        if ob is not None:
+            of._pcg_bf16 = (ob, of._version)
+        return of
     if narrow:
         fb = to_bf16(feats)
         want_bf16 = out in ("bf16", "both")
