@@ -125,16 +125,36 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             const uint32_t fb = smem_u32(full_bar + s);
             const uint32_t a_base = base + (uint32_t)s * stage_bytes;
             mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
-            if (lane == 0) {
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"((uint32_t)subs * (SUB_A + sub_b)) : "memory");
-            }
-            __syncwarp();
+            // Quads (4 consecutive rows = one gather4) with no neighbour at all cost a TMA slot like any other, and sparse maps
+            // (strided / transposed: 12-35 % dense) are mostly such quads: skip their gather and let the warp zero the
+            // 4 rows itself (32 lanes x 16 B).  The stage's expect_tx shrinks accordingly; the arrive comes after the
+            // generic-proxy zero stores + proxy fence, so the MMA thread's wait covers them too.
+            uint32_t tx_bytes = 0;
+            bool zeroed = false;
 #pragma unroll
-            for (int g = 0; g < G; ++g)
-                if (g < subs) tma_gather4(a_base + g * SUB_A + (uint32_t)lane * 4u * RB, &tm, cc * TC_KCHUNK, idx[g], fb);
+            for (int g = 0; g < G; ++g) {
+                if (g < subs) {
+                    const bool empty_quad = (idx[g].x & idx[g].y & idx[g].z & idx[g].w) < 0;
+                    uint32_t em = __ballot_sync(0xffffffffu, empty_quad);
+                    tx_bytes += (32u - (uint32_t)__popc(em)) * 4u * RB + sub_b;
+                    if (!empty_quad) tma_gather4(a_base + g * SUB_A + (uint32_t)lane * 4u * RB, &tm, cc * TC_KCHUNK, idx[g], fb);
+                    zeroed |= em != 0;
+                    while (em) {
+                        const uint32_t q = (uint32_t)__ffs(em) - 1u;
+                        em &= em - 1u;
+                        if (lane * 16u < 4u * RB)
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(a_base + g * SUB_A + q * 4u * RB + (uint32_t)lane * 16u), "r"(0u) : "memory");
+                    }
+                }
+            }
             if (lane < subs) {
                 const int k = (RB == 128 ? active[a] : active[it * G + lane]);
                 bulk_g2s(a_base + TC_A_BYTES + lane * sub_b, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
+            }
+            if (zeroed) fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
             }
             // advance this warp's cursor by P items and prefetch the next item's neighbour indices
             s += P;

@@ -332,40 +332,42 @@ extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int
 }
 
 // ---------------------------------------------------------------------------- kernel map
-// One CTA = one 128-row output tile; thread r owns row r and walks all K offsets, so the
-// coordinate is loaded once (int4) and nbr[k][tile rows] is written as one coalesced 512 B line.
-__global__ void __launch_bounds__(128) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
-                                                    uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
-                                                    int ksize, int K, int step, int lattice, int32_t *__restrict__ nbr,
-                                                    long pitch, uint32_t *__restrict__ tile_mask) {
+// One CTA = one 128-row output tile x KM_SLICES offset slices: thread (r, s) owns row r and walks offsets s, s+S, ...
+// (the coordinate is one int4 load; nbr[k][tile rows] is written as one coalesced 512 B line per offset).  Slicing the
+// offsets over threadIdx.y shortens the chain of dependent table probes per thread 4x and fills the machine on the
+// small strided sets (54 k / 13 k rows = 425 / 107 tiles), where one thread per row left most SMs idle.
+#define KM_SLICES 4
+__global__ void __launch_bounds__(128 * KM_SLICES) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
+                                                                uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
+                                                                int ksize, int K, int step, int lattice, int32_t *__restrict__ nbr,
+                                                                long pitch, uint32_t *__restrict__ tile_mask) {
     long o = (long)blockIdx.x * 128 + threadIdx.x;
     bool live = o < n_out;
     int4 c = live ? pcg_ld_coord(out_coords, o) : make_int4(0, 0, 0, 0);
     __shared__ uint32_t smask[4];
-    if (threadIdx.x < 4) smask[threadIdx.x] = 0;
+    if (threadIdx.y == 0 && threadIdx.x < 4) smask[threadIdx.x] = 0;
     __syncthreads();
     const int lo = (ksize & 1) ? -(ksize >> 1) : 0;
-    int k = 0;
-    for (int iz = 0; iz < ksize; ++iz)
-        for (int iy = 0; iy < ksize; ++iy)
-            for (int ix = 0; ix < ksize; ++ix, ++k) {
-                int row = -1;
-                if (live) {
-                    int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
-                    // lattice > 0: input rows only exist on multiples of `lattice` (transposed conv onto a finer
-                    // grid), so most offsets cannot hit for a given output parity -- no probe needed
-                    bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
-                    if (possible && pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
-                }
-                nbr[(long)k * pitch + o] = row;      // rows past n_out are the -1 padding of the last tile
-                if (tile_mask) {
-                    unsigned any = __ballot_sync(0xffffffffu, row >= 0);
-                    if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
-                }
-            }
+    const int k2 = ksize * ksize;
+    for (int k = threadIdx.y; k < K; k += KM_SLICES) {
+        const int iz = k / k2, iy = (k - iz * k2) / ksize, ix = k - iz * k2 - iy * ksize;
+        int row = -1;
+        if (live) {
+            int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
+            // lattice > 0: input rows only exist on multiples of `lattice` (transposed conv onto a finer
+            // grid), so most offsets cannot hit for a given output parity -- no probe needed
+            bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
+            if (possible && pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
+        }
+        nbr[(long)k * pitch + o] = row;      // rows past n_out are the -1 padding of the last tile
+        if (tile_mask) {
+            unsigned any = __ballot_sync(0xffffffffu, row >= 0);
+            if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
+        }
+    }
     if (tile_mask) {
         __syncthreads();
-        if (threadIdx.x < 4) tile_mask[(long)blockIdx.x * 4 + threadIdx.x] = smask[threadIdx.x];
+        if (threadIdx.y == 0 && threadIdx.x < 4) tile_mask[(long)blockIdx.x * 4 + threadIdx.x] = smask[threadIdx.x];
     }
 }
 
@@ -380,7 +382,7 @@ extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long ca
                   pcg_nbr_pitch(n_out));
     if (n_out <= 0) return 0;
     int step = transposed ? -ts : ts;
-    k_kernel_map<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
+    k_kernel_map<<<(unsigned)cdiv(n_out, 128), dim3(128, KM_SLICES), 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
                                                                            ksize, K, step, in_lattice, nbr, nbr_pitch, tile_mask);
     PCG_LAUNCHED();
     return 0;

@@ -121,11 +121,119 @@ __global__ void __launch_bounds__(256) k_gdn(const float *__restrict__ x, long n
     }
 }
 
+// Tensor-core version for C a multiple of 32 (<= 128): norm = beta + |x| @ gamma^T on mma.sync.m16n8k8 TF32 with the 3xTF32
+// split (a_hi*b_hi + a_lo*b_hi + a_hi*b_lo, fp32 accumulate: ~2^-21 relative, i.e. fp32-grade -- a plain bf16/TF32
+// product would perturb every quantised symbol downstream).  One warp = 16 rows x all C columns; lane (g, t) loads
+// channels [32q+8t, +8) of rows g and g+8 as two float4 and uses them as the A fragments of four k8 steps (k-step j:
+// slot t <- channel 32q+8t+j, slot t+4 <- channel 32q+8t+4+j); gamma sits in shared memory in the matching fragment
+// order.  The op is bound by reading and writing x (8 B per element), not by the 2*N*C^2 FLOPs.
+__device__ __forceinline__ uint32_t f2tf32(float f) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(f));
+    return r;
+}
+__device__ __forceinline__ void mma_1688_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <int C>
+__global__ void __launch_bounds__(256) k_gdn_mma(const float *__restrict__ x, long n, const float *__restrict__ beta,
+                                                 const float *__restrict__ gamma, int inverse, float *__restrict__ out) {
+    constexpr int Q = C / 32, NT = C / 8;
+    extern __shared__ float2 bs[];                  // [Q][4][NT][32]: {gamma[n][32q+8t+j], gamma[n][32q+8t+4+j]}, n = nt*8+g
+    for (int i = threadIdx.x; i < Q * 4 * NT * 32; i += blockDim.x) {
+        const int lane = i & 31, nt = (i >> 5) % NT, j = ((i >> 5) / NT) & 3, q = (i >> 5) / (NT * 4);
+        const int g = lane >> 2, t = lane & 3, nn = nt * 8 + g;
+        bs[i] = make_float2(__ldg(gamma + (long)nn * C + 32 * q + 8 * t + j), __ldg(gamma + (long)nn * C + 32 * q + 8 * t + 4 + j));
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // persistent: one CTA per SM walks the 128-row tiles, so the 64 KiB fragment image of gamma is built once per SM
+    for (long tile = blockIdx.x; tile * 128 < n; tile += gridDim.x) {
+    const long row0 = (tile * 8 + (threadIdx.x >> 5)) * 16;
+    if (row0 >= n) continue;
+    const long r0 = row0 + g, r1 = row0 + g + 8;
+    const bool ok0 = r0 < n, ok1 = r1 < n;
+    float acc[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[nt][c] = 0.f;
+#pragma unroll 1
+    for (int q = 0; q < Q; ++q) {
+        float xa[2][8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 u0 = ok0 ? __ldg(reinterpret_cast<const float4 *>(x + r0 * C + 32 * q + 8 * t) + h) : z;
+            const float4 u1 = ok1 ? __ldg(reinterpret_cast<const float4 *>(x + r1 * C + 32 * q + 8 * t) + h) : z;
+            xa[0][4 * h] = fabsf(u0.x); xa[0][4 * h + 1] = fabsf(u0.y); xa[0][4 * h + 2] = fabsf(u0.z); xa[0][4 * h + 3] = fabsf(u0.w);
+            xa[1][4 * h] = fabsf(u1.x); xa[1][4 * h + 1] = fabsf(u1.y); xa[1][4 * h + 2] = fabsf(u1.z); xa[1][4 * h + 3] = fabsf(u1.w);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            // A fragment: a0 = (row g, slot t), a1 = (row g+8, slot t), a2 = (row g, slot t+4), a3 = (row g+8, slot t+4)
+            const float af[4] = {xa[0][j], xa[1][j], xa[0][4 + j], xa[1][4 + j]};
+            uint32_t ah[4], al[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ah[i] = f2tf32(af[i]);
+                al[i] = f2tf32(af[i] - __uint_as_float(ah[i]));
+            }
+            const float2 *bq = bs + ((q * 4 + j) * NT) * 32 + lane;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                const float2 b = bq[nt * 32];
+                const uint32_t bh0 = f2tf32(b.x), bh1 = f2tf32(b.y);
+                const uint32_t bl0 = f2tf32(b.x - __uint_as_float(bh0)), bl1 = f2tf32(b.y - __uint_as_float(bh1));
+                mma_1688_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
+                mma_1688_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
+                mma_1688_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+            }
+        }
+    }
+    // C fragment: c0,c1 = (row g, cols 2t,2t+1), c2,c3 = (row g+8, same), n tile nt adds 8 columns
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        const int col = nt * 8 + 2 * t;
+        const float2 bt = __ldg(reinterpret_cast<const float2 *>(beta + col));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const long r = h ? r1 : r0;
+            if (!(h ? ok1 : ok0)) continue;
+            const float2 xv = __ldg(reinterpret_cast<const float2 *>(x + r * C + col));
+            const float n0 = acc[nt][2 * h] + bt.x, n1 = acc[nt][2 * h + 1] + bt.y;
+            float2 o;
+            o.x = inverse ? xv.x * n0 : xv.x * (1.0f / n0);
+            o.y = inverse ? xv.y * n1 : xv.y * (1.0f / n1);
+            *reinterpret_cast<float2 *>(out + r * C + col) = o;
+        }
+    }
+    }
+}
+
+template <int C>
+static int launch_gdn_mma(const float *x, long n, const float *beta, const float *gamma, int inverse, float *out, cudaStream_t st) {
+    const size_t smem = (size_t)(C / 32) * 4 * (C / 8) * 32 * sizeof(float2);
+    PCG_CUDA(cudaFuncSetAttribute(k_gdn_mma<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long tiles = cdiv(n, 128);
+    k_gdn_mma<C><<<(unsigned)(tiles < 2 * PCG_SMS ? tiles : 2 * PCG_SMS), 256, smem, st>>>(x, n, beta, gamma, inverse, out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 extern "C" int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
                            void *stream) {
     if (n <= 0) return 0;
+    cudaStream_t st = as_stream(stream);
+    const bool aligned = (((uintptr_t)x | (uintptr_t)out) & 15) == 0 && ((uintptr_t)beta & 7) == 0;
+    if (aligned && c == 128) return launch_gdn_mma<128>(x, n, beta, gamma, inverse, out, st);
+    if (aligned && c == 64) return launch_gdn_mma<64>(x, n, beta, gamma, inverse, out, st);
+    if (aligned && c == 32) return launch_gdn_mma<32>(x, n, beta, gamma, inverse, out, st);
     dim3 grid((unsigned)cdiv(n, 64), (unsigned)cdiv(c, 64));
-    k_gdn<<<grid, 256, 0, as_stream(stream)>>>(x, n, c, beta, gamma, inverse, out);
+    k_gdn<<<grid, 256, 0, st>>>(x, n, c, beta, gamma, inverse, out);
     PCG_LAUNCHED();
     return 0;
 }
