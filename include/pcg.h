@@ -125,6 +125,12 @@ int pcg_pack_weights_bf16(const float *weight, int K, int cin, int cout, void *w
 int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
                     const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
                     int act, float *out_f32, void *out_bf16, void *stream);
+/* Layers with 128-byte operand rows (cin >= 33) and cout padded to a multiple of 32 run on the LSU-gather kernel
+ * (k_conv_tc_mt: 16-byte cp.async gathers, one or two output tiles per CTA sharing each weight slice); grids of at least
+ * `tiles` 128-row tiles take the two-tile form (default 4 x 148, env PCG_TC_MT_TILES).  0 = use the TMA gather4 kernel
+ * for everything; < 0 = query only.  Returns the previous threshold.  Results do not depend on it (same per-element
+ * accumulation order in every variant). */
+long pcg_tc_set_mt_min_tiles(long tiles);
 int pcg_f32_to_bf16(const float *src, void *dst, long n, void *stream);
 /* n rows of c floats -> n rows of c_padded >= c bf16, zero padded. */
 int pcg_f32_to_bf16_rows(const float *src, long n, int c, int c_padded, void *dst, void *stream);

@@ -81,6 +81,48 @@ def test_tc_path_is_exact_on_bf16_representable_inputs(pkg, dev):
             assert np.array_equal(out.cpu().numpy(), ref), f"{mode} cin={cin} cout={cout}: max |d| = {np.abs(out.cpu().numpy() - ref).max()}"
 
 
+def test_two_tiles_per_cta_kernel_equals_single_tile_kernel(pkg, dev):
+    """k_conv_tc_mt (two output tiles per CTA sharing each weight slice; taken by large grids) forced on small inputs:
+    bit-exact on integer operands against the fp32 oracle, and bit-identical to the one-tile kernel on random operands
+    (same per-element accumulation order), including an odd number of tiles and strided / transposed maps."""
+    so = pkg.sparse_ops
+    lib = pkg._lib.load()
+    rng = np.random.default_rng(3)
+    C, cs = setup(dev, pkg, seed=21, scale=2)
+    assert (len(C) + 127) // 128 >= 9
+    down = cs.strided(2)
+    up = down.generated(2, 2)
+    cases = [(cs, cs, 3, False, 128, 64), (cs, cs, 3, False, 192, 256), (cs, cs, 3, False, 64, 32), (cs, down, 5, False, 128, 128),
+             (down, up, 2, True, 192, 192), (cs, cs, 1, False, 512, 128)]
+    prev_mode = so.set_conv_mode("tc")
+    try:
+        for in_set, out_set, ksize, transposed, cin, cout in cases:
+            K = ksize ** 3
+            Fi = rng.integers(-4, 5, (in_set.n, cin)).astype(np.float32)
+            Wi = rng.integers(-2, 3, (K, cin, cout)).astype(np.float32)
+            bi = rng.integers(-3, 4, (1, cout)).astype(np.float32)
+            Fr = torch.from_numpy(rng.standard_normal((in_set.n, cin)).astype(np.float32)).to(dev)
+            Wr = torch.from_numpy((rng.standard_normal((K, cin, cout)) * 0.1).astype(np.float32)).to(dev)
+            wi = torch.from_numpy(Wi if K > 1 else Wi[0]).to(dev)
+            wr = Wr if K > 1 else Wr[0]
+            res = {}
+            for tiles in (0, 1):            # 0 = never (one tile per CTA), 1 = always
+                prev = lib.pcg_tc_set_mt_min_tiles(tiles)
+                try:
+                    res[tiles] = (so.sparse_conv(torch.from_numpy(Fi).to(dev), in_set, out_set, wi, torch.from_numpy(bi).to(dev), ksize, transposed),
+                                  so.sparse_conv(Fr, in_set, out_set, wr, None, ksize, transposed, act=so.ACT_RELU))
+                finally:
+                    lib.pcg_tc_set_mt_min_tiles(prev)
+            ts_o = out_set.ts if transposed else in_set.ts
+            ref = oracle_conv(in_set.coords.cpu().numpy(), out_set.coords.cpu().numpy(), Fi, Wi, bi, ksize, ts_o, transposed)
+            tag = f"k{ksize} {cin}->{cout} transposed={transposed}"
+            assert np.array_equal(res[1][0].cpu().numpy(), ref), tag
+            assert torch.equal(res[0][0], res[1][0]), tag
+            assert torch.equal(res[0][1], res[1][1]), tag
+    finally:
+        so.set_conv_mode(prev_mode)
+
+
 @pytest.mark.parametrize("mode", ["f32", "tc"])
 def test_conv_is_run_to_run_and_order_deterministic(pkg, dev, mode):
     """Fact 9: encoder and decoder must reproduce h_s bit-for-bit.  Same inputs -> same bits; and a row's result

@@ -41,7 +41,7 @@ def run(name, in_set, out_set, cin, cout, ksize, reps=5):
         so.sparse_conv(fb, in_set, out_set, w, None, ksize, False, packed=pw, out="bf16" if cout % 16 == 0 else "f32")
         e1.record()
         torch.cuda.synchronize()
-        if i >= 2:
+        if i >= 2 or reps == 0:
             ts.append(e0.elapsed_time(e1))
     ms = sorted(ts)[len(ts) // 2]
     print(f"{name:<34} n_out={out_set.n:>8} pairs/row={pairs / out_set.n:5.1f}  {ms:7.3f} ms  {2e-9 * pairs * cin * cout / ms:7.1f} TF/s "
@@ -49,8 +49,13 @@ def run(name, in_set, out_set, cin, cout, ksize, reps=5):
 
 
 so.set_conv_mode("tc")
-print("PCG_TC_STAGES=%s PCG_TC_SMEM_KB=%s" % (os.environ.get("PCG_TC_STAGES"), os.environ.get("PCG_TC_SMEM_KB")))
+print("PCG_TC_GATHER=%s PCG_TC_STAGES=%s PCG_TC_SMEM_KB=%s" % (os.environ.get("PCG_TC_GATHER"), os.environ.get("PCG_TC_STAGES"), os.environ.get("PCG_TC_SMEM_KB")))
+QUICK = "--quick" in sys.argv          # two launches per shape, first two shapes only (for ncu captures)
 with torch.no_grad():
+    if QUICK:
+        run("27x128x64  stride-1 set (818k)", cs1, cs1, 128, 64, 3, reps=0)
+        run("27x192x256 stride-2 set (214k)", cs2, cs2, 192, 256, 3, reps=0)
+        sys.exit(0)
     run("27x128x64  stride-1 set (818k)", cs1, cs1, 128, 64, 3)
     run("27x128x128 stride-1 set (818k)", cs1, cs1, 128, 128, 3)
     run("27x192x256 stride-2 set (214k)", cs2, cs2, 192, 256, 3)

@@ -22,6 +22,7 @@ _PROTOS = {
     "pcg_hash_capacity": (_L, [_L]),
     "pcg_nbr_pitch": (_L, [_L]),
     "pcg_tc_cin_padded": (_I, [_I]),
+    "pcg_tc_set_mt_min_tiles": (_L, [_L]),
     "pcg_scratch_bytes": (_SZ, [_L]),
     "pcg_hash_build": (_I, [_P, _L, _P, _P, _L, _P]),
     "pcg_hash_lookup": (_I, [_P, _P, _L, _P, _L, _P, _P]),

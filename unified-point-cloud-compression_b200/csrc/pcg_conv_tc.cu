@@ -17,6 +17,7 @@
 // is one fixed-order chain of MMAs over ascending (k, cin-chunk): bit-reproducible, and independent of which
 // tile a row lands in (absent neighbours contribute exact zeros).
 #include <stdlib.h>
+#include <string.h>
 
 #include "pcg_tc.cuh"
 
@@ -33,6 +34,8 @@ struct TcParams {
     const float *bias;
     float *out_f32;
     __nv_bfloat16 *out_bf16;
+    const uint8_t *feats;         // bf16 operand rows (LSU gather mode)
+    long row_bytes;               // bytes per operand row = 2 * cin_p
     long n_out, nbr_pitch;
     int cout, cout_p, K;
     int chunks;      // RB == 128: 64-wide K chunks per kernel offset; otherwise 1
@@ -41,8 +44,66 @@ struct TcParams {
     int act;
 };
 
-template <int RB>
+// epilogue piece shared by the tcgen05 conv kernels: 16 accumulator columns [c0, c0+16) of output row o -> bias, activation, fp32 and/or bf16
+__device__ __forceinline__ void tc_store16(const TcParams &p, long o, int c0, const uint32_t (&v)[16]) {
+    float f[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+        f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
+    if ((p.cout & 15) == 0) {
+        if (p.out_f32) {
+            float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        }
+        if (p.out_bf16) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                pk[j] = *reinterpret_cast<uint32_t *>(&h);
+            }
+            uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
+            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        }
+    } else if (p.out_f32) {   // narrow heads (cout = 1, 3, ...): scalar stores of the real columns
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
+    }
+}
+
+// LSU gather of one 128-row x 128-byte operand sub-tile into its 128B-swizzled image at dst_tile.  Lane m holds the neighbour
+// indices of rows m, 32+m, 64+m, 96+m in idx[0..3]; a warp instruction copies rows 4j..4j+3 (8 lanes x 16 B each).  A producer
+// warp is alone on its scheduler, so every instruction costs its full latency: the copy is kept to shuffle + compare + one
+// 32x32->64 multiply-add + cp.async (absent rows: src-size 0 zero-fills and the source address is never dereferenced; the
+// destination offsets are two per-lane constants + immediates since (row & 7) = 4 (u & 1) + q).
+__device__ __forceinline__ int tc_shfl_idx(int v, int src_lane) {      // volatile: keeps the batch order written below
+    int r;
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(v), "r"(src_lane));
+    return r;
+}
+__device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint8_t *fcol, int row_bytes, const int (&idx)[4], int lane) {
+    const int q = lane >> 3, c16 = lane & 7;
+    const uint32_t d0 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ q) << 4);
+    const uint32_t d1 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ (4 + q)) << 4);
+    asm volatile("" : "+l"(fcol));        // keep the column base one 64-bit addend of the multiply-add below
+#pragma unroll
+    for (int jb = 0; jb < 4; ++jb) {
+        int src[8];                       // eight shuffles in flight, then eight copies: the latencies overlap instead of adding up
+#pragma unroll
+        for (int u = 0; u < 8; ++u) src[u] = tc_shfl_idx(idx[jb], 4 * u + q);
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            cp_async16(((u & 1) ? d1 : d0) + (uint32_t)((32 * jb + 4 * u) * 128), fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes,
+                       src[u] >= 0 ? 16u : 0u);
+    }
+}
+
+template <int RB, bool LSU>
 __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtensorMap tm, const TcParams p) {
+    static_assert(!LSU || RB == 128, "the LSU gather is written for 128-byte operand rows");
     constexpr int G = 128 / RB;                  // operand sub-tiles (kernel offsets) per 16 KiB stage
     constexpr uint32_t SUB_A = TC_ROWS * RB;     // bytes of one A sub-tile
     extern __shared__ uint8_t smem_raw[];
@@ -65,7 +126,8 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            mbar_init(smem_u32(full_bar + s), 1);         // one arrive.expect_tx; data arrives as tx bytes
+            // TMA gather: one arrive.expect_tx, data arrives as tx bytes.  LSU gather: + one cp.async-completion arrive per lane
+            mbar_init(smem_u32(full_bar + s), LSU ? 33 : 1);
             mbar_init(smem_u32(empty_bar + s), 1);        // one tcgen05.commit
         }
         mbar_init(smem_u32(accum_bar), 1);
@@ -119,8 +181,43 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                                        : make_int4(-1, -1, -1, -1);
             }
         };
-        if (warp < P && warp < n_items) load_idx(warp, a);
-        for (int it = warp; warp < P && it < n_items; it += P) {
+        if constexpr (LSU) {
+            // ---- LSU gather (RB == 128): 16-byte cp.async (LDGSTS) straight into the swizzled operand image.  One warp
+            // instruction moves 4 rows x 128 B (8 lanes per row: 4 L1 wavefronts), so a row costs ~1 LSU cycle instead of the
+            // ~4 cycles a TMA gather4 row request retires in; absent neighbours are src-size 0 = zero fill (no traffic).
+            // Lane m holds the neighbour indices of rows m, 32+m, 64+m, 96+m; instruction j needs row 4j + (lane >> 3):
+            // one shuffle from lane (4j + q) & 31 of register j >> 3.
+            const int c16 = lane & 7;
+            const int32_t *nbr_t = p.nbr + tile * TC_ROWS + lane;
+            const uint8_t *fsrc = p.feats + c16 * 16;
+            int idx4[4];
+            auto load_idx4 = [&](int a_) {
+                const int32_t *nb = nbr_t + (long)active[a_] * p.nbr_pitch;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) idx4[t] = __ldg(nb + 32 * t);
+            };
+            if (warp < P && warp < n_items) load_idx4(a);
+            for (int it = warp; warp < P && it < n_items; it += P) {
+                const uint32_t fb = smem_u32(full_bar + s);
+                const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+                mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
+                if (lane == 0) {
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(sub_b) : "memory");
+                    bulk_g2s(a_base + TC_A_BYTES, p.wpacked + ((size_t)active[a] * p.chunks + cc) * sub_b, sub_b, fb);
+                }
+                const uint8_t *fcol = fsrc + cc * 128;
+                tc_lsu_gather_tile(a_base, fcol, (int)p.row_bytes, idx4, lane);
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
+                const int a_prev = a;
+                s += P;
+                while (s >= p.stages) { s -= p.stages; ++wrap; }
+                cc += P;
+                while (cc >= p.chunks) { cc -= p.chunks; ++a; }
+                if (it + P < n_items && a != a_prev) load_idx4(a);
+            }
+        }
+        if (!LSU && warp < P && warp < n_items) load_idx(warp, a);
+        for (int it = warp; !LSU && warp < P && it < n_items; it += P) {
             const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;     // sub-tiles in this item
             const uint32_t fb = smem_u32(full_bar + s);
             const uint32_t a_base = base + (uint32_t)s * stage_bytes;
@@ -178,34 +275,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] = 0u;
             }
-            if (live) {
-                float f[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
-                if ((p.cout & 15) == 0) {
-                    if (p.out_f32) {
-                        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-                    }
-                    if (p.out_bf16) {
-                        uint32_t pk[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
-                            pk[j] = *reinterpret_cast<uint32_t *>(&h);
-                        }
-                        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
-                        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    }
-                } else if (p.out_f32) {   // narrow heads (cout = 1, 3, ...): scalar stores of the real columns
-#pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
-                }
-            }
+            if (live) tc_store16(p, o, c0, v);
         }
         tc_fence_before();
     } else {
@@ -217,6 +287,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             for (int it = 0; it < n_items; ++it) {
                 const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;
                 mbar_wait(smem_u32(full_bar + s), ph);
+                if (LSU) fence_proxy_async();        // cp.async wrote the operand rows through the generic proxy
                 tc_fence_after();
                 const uint32_t a_addr = base + (uint32_t)s * stage_bytes;
 #pragma unroll
@@ -237,6 +308,177 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
     }
     __syncthreads();
     if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)p.tmem_cols) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------- T output tiles per CTA
+// The single-tile kernel re-fetches the 128 x cout_p weight slice of every (offset, chunk) for every 128-row tile: for
+// cout_p >= 64 that is as many L2 bytes as the gathered rows themselves, and the kernel runs at the L2 -> SM bandwidth
+// (~9 TB/s measured, profiles/r01_conv_l2_model.md).  Here one CTA owns T adjacent tiles: a pipeline stage holds T gathered
+// 128-row operand sub-tiles and ONE weight slice, the MMA thread issues T accumulations (TMEM columns t*cout_p) against the
+// same B descriptor.  LSU gather (16-byte cp.async into the 128B-swizzled image) as in k_conv_tc<128, true>; a tile that does
+// not use an offset skips both its gather and its MMAs.  Per-element accumulation order is unchanged (ascending offset, chunk).
+template <int T>
+__global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p) {
+    constexpr int MMA_WARP = 4 * T;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t *sm = smem_raw + (base - raw);
+    const uint32_t sub_b = (uint32_t)p.cout_p * 128u;
+    const uint32_t stage_bytes = T * TC_A_BYTES + sub_b;
+    uint8_t *ctl = sm + (size_t)p.stages * stage_bytes;
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(ctl);
+    uint64_t *empty_bar = full_bar + TC_MAX_STAGES;
+    uint64_t *accum_bar = empty_bar + TC_MAX_STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_bar + 1);
+    int *n_active_s = reinterpret_cast<int *>(tmem_slot + 1);
+    uint32_t *tmask_s = reinterpret_cast<uint32_t *>(n_active_s + 1);   // [T][4]
+    uint8_t *active = reinterpret_cast<uint8_t *>(tmask_s + 4 * T);     // [128]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long tile0 = (long)blockIdx.x * T;
+    const long n_tiles = (p.n_out + TC_ROWS - 1) / TC_ROWS;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(smem_u32(full_bar + s), 32 * T + 1);   // one cp.async-completion arrive per producer lane + the weight slice's expect_tx
+            mbar_init(smem_u32(empty_bar + s), 1);
+        }
+        mbar_init(smem_u32(accum_bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < TC_ROWS) {
+        uint32_t u[4] = {0u, 0u, 0u, 0u};                 // union of the T tiles' offset masks
+#pragma unroll
+        for (int t = 0; t < T; ++t)
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const uint32_t m = tile0 + t < n_tiles ? __ldg(p.tile_mask + (tile0 + t) * 4 + w) : 0u;
+                u[w] |= m;
+                if (tid == 0) tmask_s[t * 4 + w] = m;
+            }
+        const uint32_t w = tid >> 5, b = tid & 31;
+        const uint32_t mine = w == 0 ? u[0] : (w == 1 ? u[1] : (w == 2 ? u[2] : u[3]));
+        if (tid < p.K && ((mine >> b) & 1u)) {
+            int pos = __popc(mine & ((1u << b) - 1u));
+            if (w > 0) pos += __popc(u[0]);
+            if (w > 1) pos += __popc(u[1]);
+            if (w > 2) pos += __popc(u[2]);
+            active[pos] = (uint8_t)tid;
+        }
+        if (tid == 0) *n_active_s = __popc(u[0]) + __popc(u[1]) + __popc(u[2]) + __popc(u[3]);
+    }
+    if (warp == MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_d = *tmem_slot;
+    const int n_active = *n_active_s;
+    const int n_items = n_active * p.chunks;
+    auto uses = [&](int t, int k) -> bool { return (tmask_s[t * 4 + (k >> 5)] >> (k & 31)) & 1u; };
+
+    if (warp < MMA_WARP) {
+        // ------------------------------------------------------------------ producers: warp (g, t) gathers tile t of items g, g+P, ...
+        const int g = warp & 3, t = warp >> 2;
+        const int P = p.stages < 4 ? p.stages : 4;
+        int s = g, wrap = 0;
+        while (s >= p.stages) { s -= p.stages; ++wrap; }
+        int a = 0, cc = g;
+        while (cc >= p.chunks) { cc -= p.chunks; ++a; }
+        const int32_t *nbr_t = p.nbr + (tile0 + t) * TC_ROWS + lane;
+        const uint8_t *fsrc = p.feats + (lane & 7) * 16;
+        const int row_bytes = (int)p.row_bytes;
+        int idx4[4];
+        auto load_idx4 = [&](int a_) {
+            const int k = active[a_];
+            if (uses(t, k)) {
+                const int32_t *nb = nbr_t + (long)k * p.nbr_pitch;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) idx4[u] = __ldg(nb + 32 * u);
+            }
+        };
+        if (g < P && g < n_items) load_idx4(a);
+        for (int it = g; g < P && it < n_items; it += P) {
+            const int k = active[a];
+            const uint32_t fb = smem_u32(full_bar + s);
+            const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+            mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
+            if (t == 0 && lane == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(sub_b) : "memory");
+                bulk_g2s(a_base + T * TC_A_BYTES, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
+            }
+            if (uses(t, k)) tc_lsu_gather_tile(a_base + (uint32_t)t * TC_A_BYTES, fsrc + cc * 128, row_bytes, idx4, lane);
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
+            const int a_prev = a;
+            s += P;
+            while (s >= p.stages) { s -= p.stages; ++wrap; }
+            cc += P;
+            while (cc >= p.chunks) { cc -= p.chunks; ++a; }
+            if (it + P < n_items && a != a_prev) load_idx4(a);
+        }
+
+        // ------------------------------------------------------------------ epilogue: warp (g, t) stores rows 32g..32g+31 of tile t
+        if (n_items > 0) {
+            mbar_wait(smem_u32(accum_bar), 0);
+            tc_fence_after();
+        }
+        const long o = (tile0 + t) * TC_ROWS + g * 32 + lane;
+        const bool live = o < p.n_out;
+        const bool has = (tmask_s[t * 4] | tmask_s[t * 4 + 1] | tmask_s[t * 4 + 2] | tmask_s[t * 4 + 3]) != 0u;
+        const uint32_t lane_base = tmem_d + ((uint32_t)(g * 32) << 16) + (uint32_t)(t * p.cout_p);
+        if (tile0 + t < n_tiles) {
+            for (int c0 = 0; c0 < p.cout; c0 += 16) {
+                uint32_t v[16];
+                if (has) tmem_ld16(lane_base + (uint32_t)c0, v);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = 0u;
+                }
+                if (live) tc_store16(p, o, c0, v);
+            }
+        }
+        tc_fence_before();
+    } else {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.cout_p >> 3) << 17) | ((TC_ROWS >> 4) << 24);
+            int s = 0, a = 0, cc = 0;
+            uint32_t ph = 0, started = 0;
+            for (int it = 0; it < n_items; ++it) {
+                const int k = active[a];
+                mbar_wait(smem_u32(full_bar + s), ph);
+                fence_proxy_async();                 // cp.async wrote the operand rows through the generic proxy
+                tc_fence_after();
+                const uint32_t a_addr = base + (uint32_t)s * stage_bytes;
+                const uint64_t bdesc = umma_desc<128>(a_addr + T * TC_A_BYTES);
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    if (!uses(t, k)) continue;
+                    const uint64_t adesc = umma_desc<128>(a_addr + t * TC_A_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk)
+                        umma_bf16(tmem_d + (uint32_t)(t * p.cout_p), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc,
+                                  (((started >> t) & 1u) | (uint32_t)kk) ? 1u : 0u);
+                    started |= 1u << t;
+                }
+                umma_commit(smem_u32(empty_bar + s));
+                if (++s == p.stages) { s = 0; ph ^= 1u; }
+                if (++cc == p.chunks) { cc = 0; ++a; }
+            }
+            if (n_items > 0) umma_commit(smem_u32(accum_bar));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    if (warp == MMA_WARP) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)p.tmem_cols) : "memory");
     }
@@ -303,10 +545,23 @@ PcgEncodeTiled pcg_tensor_map_encoder() {
 
 extern "C" int pcg_tc_cin_padded(int cin) { return tc_cin_p(cin); }
 
-template <int RB>
+// grids of at least this many 128-row tiles take the two-tiles-per-CTA kernel (0 = never); env PCG_TC_MT_TILES or
+// pcg_tc_set_mt_min_tiles() (tests force the path on small inputs)
+static long g_mt_min_tiles = -1;
+static long tc_mt_min_tiles() {
+    if (g_mt_min_tiles < 0) g_mt_min_tiles = getenv("PCG_TC_MT_TILES") ? atol(getenv("PCG_TC_MT_TILES")) : 4L * PCG_SMS;
+    return g_mt_min_tiles;
+}
+extern "C" long pcg_tc_set_mt_min_tiles(long tiles) {
+    const long prev = tc_mt_min_tiles();
+    if (tiles >= 0) g_mt_min_tiles = tiles;
+    return prev;
+}
+
+template <int RB, bool LSU>
 static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cudaStream_t st) {
-    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_tc<RB><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
+    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB, LSU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_conv_tc<RB, LSU><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
     PCG_LAUNCHED();
     return 0;
 }
@@ -345,6 +600,41 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.n_out = n_out; p.cout = cout; p.cout_p = tc_cout_p(cout); p.K = K;
     p.chunks = rb == 128 ? (cin_p + 63) / 64 : 1;
     p.act = act;
+    p.feats = reinterpret_cast<const uint8_t *>(feats_bf16);
+    p.row_bytes = (long)cin_p * 2;
+    cudaStream_t st = as_stream(stream);
+    if (rb == 128 && (p.cout_p & 31) == 0 && tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma"))) {
+        // 128-byte operand rows: LSU-gather kernel.  Static shape rule (measured with tools/bench_conv.py, profiles/r01_conv_variants.md):
+        //   wide outputs (weight slice >= 24 KiB per stage)  two tiles per CTA, one CTA per SM, deep ring
+        //   large grids                                      two tiles per CTA, two CTAs per SM (16 producer warps per SM)
+        //   small grids                                      one tile per CTA, three CTAs per SM (most independent pipelines)
+        static const int mt_t = getenv("PCG_TC_MT_T") ? atoi(getenv("PCG_TC_MT_T")) : 0;          // tuning knobs: force T / the smem budget
+        static const int mt_kb = getenv("PCG_TC_MT_SMEM_KB") ? atoi(getenv("PCG_TC_MT_SMEM_KB")) : 0;
+        const long tiles = cdiv(n_out, TC_ROWS);
+        int T, kb;
+        if (p.cout_p > 128) { T = 2; kb = 200; }
+        else if (tiles >= tc_mt_min_tiles()) { T = 2; kb = 104; }
+        else { T = 1; kb = 70; }
+        if (mt_t == 1 || mt_t == 2) T = mt_t;
+        if (mt_kb > 0) kb = mt_kb;
+        const size_t stage_bytes = (size_t)T * TC_A_BYTES + (size_t)p.cout_p * 128;
+        int stages = (int)(((size_t)kb * 1024) / stage_bytes);
+        if (stages < 2) stages = 2;
+        if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
+        p.stages = stages;
+        p.tmem_cols = 32;
+        while (p.tmem_cols < T * p.cout_p) p.tmem_cols <<= 1;
+        const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
+        if (T == 1) {
+            PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_conv_tc_mt<1><<<(unsigned)tiles, 160, smem, st>>>(p);
+        } else {
+            PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_conv_tc_mt<2><<<(unsigned)cdiv(tiles, 2), 288, smem, st>>>(p);
+        }
+        PCG_LAUNCHED();
+        return 0;
+    }
     p.tmem_cols = 32;
     while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
     const size_t stage_bytes = TC_A_BYTES + (size_t)p.cout_p * 128;
@@ -356,8 +646,9 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
-    cudaStream_t st = as_stream(stream);
-    if (rb == 32) return launch_tc<32>(tm, p, smem, st);
-    if (rb == 64) return launch_tc<64>(tm, p, smem, st);
-    return launch_tc<128>(tm, p, smem, st);
+    static const bool lsu = getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "lsu");   // A/B knob (tools/bench_conv.py)
+    if (rb == 32) return launch_tc<32, false>(tm, p, smem, st);
+    if (rb == 64) return launch_tc<64, false>(tm, p, smem, st);
+    if (lsu) return launch_tc<128, true>(tm, p, smem, st);
+    return launch_tc<128, false>(tm, p, smem, st);
 }
