@@ -300,9 +300,14 @@ def main():
         return {"launches": d["launches"], "ms": round(d["ms"], 3), "algorithmic_gb": round(d["bytes"] / 1e9, 3), "achieved_gbs": round(gbs, 1),
                 "frac_of_hbm_peak": round(gbs / pk["hbm_gbs"], 4)}
 
-    roofline = {"bound": "tensor", "kernel": "k_conv_tc + k_gemm_first (tcgen05 sparse conv kernels, all launches of one step)",
+    traffic = None                      # DRAM bytes of the same launches from the committed ncu --set full capture
+    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tp) and args.workload == "frame10":
+        traffic = json.load(open(tp))["tcgen05_conv_dram_bytes_per_step"]
+    roofline = {"bound": "tensor", "kernel": "k_conv_tc_mt / k_conv_tc + k_gemm_first (tcgen05 sparse conv kernels, all launches of one step)",
                 "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops"],
-                "traffic": None, "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
+                "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu, profiles/r01_ncu_full_v5.md)",
+                "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
                 "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms / ms_res if ms_res else None,
                 "algorithmic_gflop_per_step": tc_flops / 1e9,
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},

@@ -206,6 +206,14 @@ int pcg_topk_mask(const float *logits, const int32_t *coords, long n, int batch,
 int pcg_prune_rows(const int32_t *coords, const float *feats, long n, int c, const uint8_t *mask,
                    int32_t *out_coords, float *out_feats, int32_t *d_n_out, void *scratch,
                    size_t scratch_bytes, void *stream);
+/* Index form of the prune: ascending source rows of the kept entries of `mask` (n_out <= n), so that the caller can
+ * compose the prune with a re-ordering of the survivors (transforms.py:257-282 followed by a row permutation is free in
+ * ME semantics) and move the feature rows once with pcg_gather_rows.  scratch >= pcg_scratch_bytes(n). */
+int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
+                     void *stream);
+/* out_coords[r] = coords[rows[r]], out_feats[r] = feats[rows[r]] (c fp32 channels) for r < n_rows; either pair may be NULL. */
+int pcg_gather_rows(const int32_t *coords, const float *feats, int c, const int32_t *rows, long n_rows, int32_t *out_coords,
+                    float *out_feats, void *stream);
 
 /* ---- interpolation: SparseTensor.features_at_coordinates (ME6) ---------------------------------
  * Trilinear over the 2^3 corners at spacing ts; absent corners contribute 0.  query: nq x 4 fp32. */

@@ -138,6 +138,31 @@ def test_prune_rows(pkg, dev, n, c):
     assert (oc.cpu().numpy() == C[mask]).all() and (of.cpu().numpy() == Fm[mask]).all()
 
 
+@pytest.mark.parametrize("n,c", [(1, 3), (5000, 128), (4099, 7)])
+def test_prune_rows_reordered_equals_prune_then_morton_sort(pkg, dev, n, c):
+    """pcg_mask_to_rows + pcg_gather_rows: the fused prune + Z-order re-sort moves the same rows to the same places as
+    the order-preserving prune followed by the Morton permutation."""
+    so = pkg.sparse_ops
+    rng = np.random.default_rng(n + c)
+    C = np.unique(rng.integers(0, 60, (n, 4)).astype(np.int32), axis=0)
+    C = C[rng.permutation(len(C))]
+    C[:, 0] = 0
+    C = np.unique(C, axis=0)[rng.permutation(len(np.unique(C, axis=0)))]
+    n = len(C)
+    Fm = rng.standard_normal((n, c)).astype(np.float32)
+    mask = rng.random(n) < 0.4
+    if n == 1:
+        mask[:] = True
+    Cd, Fd, md = to_dev(C, dev), torch.from_numpy(Fm).to(dev), torch.from_numpy(mask).to(dev)
+    oc, of = so.prune_rows(Cd, Fd, md)
+    perm = so.sort_rows(oc, morton=True)
+    rc, rf = so.prune_rows_reordered(Cd, Fd, md, int(mask.sum()))
+    assert torch.equal(rc, oc[perm]) and torch.equal(rf, of[perm])
+    rows = torch.from_numpy(np.nonzero(mask)[0].astype(np.int32)).to(dev)
+    gc, gf = so.gather_rows(Cd, Fd, rows)
+    assert torch.equal(gc, oc) and torch.equal(gf, of)
+
+
 @pytest.mark.parametrize("n,k", [(10, 3), (5000, 1234), (5000, 0), (5000, 5000), (5000, 7000), (70000, 35000)])
 def test_topk_mask(pkg, dev, n, k):
     so = pkg.sparse_ops

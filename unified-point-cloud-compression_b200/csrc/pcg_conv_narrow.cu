@@ -87,10 +87,15 @@ __global__ void __launch_bounds__(256) k_conv_mma(const __nv_bfloat16 *__restric
         for (int b = 0; b < NT; ++b)
 #pragma unroll
             for (int c = 0; c < 4; ++c) acc[a][b][c] = 0.f;
-    for (int k0 = 0; k0 < K; k0 += U) {
-        int mine[U];
+    // The neighbour table is streamed from DRAM (no reuse) and every row gather depends on it: the indices of batch b+1 are
+    // requested before the rows of batch b, so the two DRAM latencies of a batch overlap instead of adding up.
+    int mine[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) mine[u] = (my_ok && k0 + u < K) ? __ldg(nbr + (long)(k0 + u) * pitch + my_row) : -1;
+    for (int u = 0; u < U; ++u) mine[u] = (my_ok && u < K) ? __ldg(nbr + (long)u * pitch + my_row) : -1;
+    for (int k0 = 0; k0 < K; k0 += U) {
+        int nxt[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) nxt[u] = (my_ok && k0 + U + u < K) ? __ldg(nbr + (long)(k0 + U + u) * pitch + my_row) : -1;
         uint4 v[U][R][V];
 #pragma unroll
         for (int u = 0; u < U; ++u)
@@ -128,6 +133,8 @@ __global__ void __launch_bounds__(256) k_conv_mma(const __nv_bfloat16 *__restric
                 }
             }
         }
+#pragma unroll
+        for (int u = 0; u < U; ++u) mine[u] = nxt[u];
     }
     // C fragment: c0,c1 = (row g, cols 2t, 2t+1), c2,c3 = (row g+8, same cols); n tile nt adds 8 columns
 #pragma unroll

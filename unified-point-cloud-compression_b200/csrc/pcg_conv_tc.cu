@@ -101,9 +101,8 @@ __device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint
     }
 }
 
-template <int RB, bool LSU>
+template <int RB>
 __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtensorMap tm, const TcParams p) {
-    static_assert(!LSU || RB == 128, "the LSU gather is written for 128-byte operand rows");
     constexpr int G = 128 / RB;                  // operand sub-tiles (kernel offsets) per 16 KiB stage
     constexpr uint32_t SUB_A = TC_ROWS * RB;     // bytes of one A sub-tile
     extern __shared__ uint8_t smem_raw[];
@@ -126,8 +125,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            // TMA gather: one arrive.expect_tx, data arrives as tx bytes.  LSU gather: + one cp.async-completion arrive per lane
-            mbar_init(smem_u32(full_bar + s), LSU ? 33 : 1);
+            mbar_init(smem_u32(full_bar + s), 1);         // one arrive.expect_tx; data arrives as tx bytes
             mbar_init(smem_u32(empty_bar + s), 1);        // one tcgen05.commit
         }
         mbar_init(smem_u32(accum_bar), 1);
@@ -181,43 +179,8 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
                                        : make_int4(-1, -1, -1, -1);
             }
         };
-        if constexpr (LSU) {
-            // ---- LSU gather (RB == 128): 16-byte cp.async (LDGSTS) straight into the swizzled operand image.  One warp
-            // instruction moves 4 rows x 128 B (8 lanes per row: 4 L1 wavefronts), so a row costs ~1 LSU cycle instead of the
-            // ~4 cycles a TMA gather4 row request retires in; absent neighbours are src-size 0 = zero fill (no traffic).
-            // Lane m holds the neighbour indices of rows m, 32+m, 64+m, 96+m; instruction j needs row 4j + (lane >> 3):
-            // one shuffle from lane (4j + q) & 31 of register j >> 3.
-            const int c16 = lane & 7;
-            const int32_t *nbr_t = p.nbr + tile * TC_ROWS + lane;
-            const uint8_t *fsrc = p.feats + c16 * 16;
-            int idx4[4];
-            auto load_idx4 = [&](int a_) {
-                const int32_t *nb = nbr_t + (long)active[a_] * p.nbr_pitch;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) idx4[t] = __ldg(nb + 32 * t);
-            };
-            if (warp < P && warp < n_items) load_idx4(a);
-            for (int it = warp; warp < P && it < n_items; it += P) {
-                const uint32_t fb = smem_u32(full_bar + s);
-                const uint32_t a_base = base + (uint32_t)s * stage_bytes;
-                mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
-                if (lane == 0) {
-                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(sub_b) : "memory");
-                    bulk_g2s(a_base + TC_A_BYTES, p.wpacked + ((size_t)active[a] * p.chunks + cc) * sub_b, sub_b, fb);
-                }
-                const uint8_t *fcol = fsrc + cc * 128;
-                tc_lsu_gather_tile(a_base, fcol, (int)p.row_bytes, idx4, lane);
-                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
-                const int a_prev = a;
-                s += P;
-                while (s >= p.stages) { s -= p.stages; ++wrap; }
-                cc += P;
-                while (cc >= p.chunks) { cc -= p.chunks; ++a; }
-                if (it + P < n_items && a != a_prev) load_idx4(a);
-            }
-        }
-        if (!LSU && warp < P && warp < n_items) load_idx(warp, a);
-        for (int it = warp; !LSU && warp < P && it < n_items; it += P) {
+        if (warp < P && warp < n_items) load_idx(warp, a);
+        for (int it = warp; warp < P && it < n_items; it += P) {
             const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;     // sub-tiles in this item
             const uint32_t fb = smem_u32(full_bar + s);
             const uint32_t a_base = base + (uint32_t)s * stage_bytes;
@@ -287,7 +250,6 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
             for (int it = 0; it < n_items; ++it) {
                 const int subs = (n_sub - it * G) < G ? (n_sub - it * G) : G;
                 mbar_wait(smem_u32(full_bar + s), ph);
-                if (LSU) fence_proxy_async();        // cp.async wrote the operand rows through the generic proxy
                 tc_fence_after();
                 const uint32_t a_addr = base + (uint32_t)s * stage_bytes;
 #pragma unroll
@@ -313,13 +275,18 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
     }
 }
 
-// ---------------------------------------------------------------------------- T output tiles per CTA
-// The single-tile kernel re-fetches the 128 x cout_p weight slice of every (offset, chunk) for every 128-row tile: for
-// cout_p >= 64 that is as many L2 bytes as the gathered rows themselves, and the kernel runs at the L2 -> SM bandwidth
-// (~9 TB/s measured, profiles/r01_conv_l2_model.md).  Here one CTA owns T adjacent tiles: a pipeline stage holds T gathered
-// 128-row operand sub-tiles and ONE weight slice, the MMA thread issues T accumulations (TMEM columns t*cout_p) against the
-// same B descriptor.  LSU gather (16-byte cp.async into the 128B-swizzled image) as in k_conv_tc<128, true>; a tile that does
-// not use an offset skips both its gather and its MMAs.  Per-element accumulation order is unchanged (ascending offset, chunk).
+// ---------------------------------------------------------------------------- LSU gather, T output tiles per CTA
+// k_conv_tc above is paced by the TMA unit: tile::gather4 retires ~4 cycles per gathered row per SM, 556 cycles per
+// 128-row stage, whatever else is idle (ncu: L2 38 %, tensor 23 %, L1 15 %).  Here the rows are gathered by the LSU instead:
+// 16-byte cp.async (LDGSTS) straight into the 128B-swizzled operand image, 8 lanes per 128-byte row, completion tracked by
+// cp.async.mbarrier.arrive.noinc on the stage's mbarrier, absent neighbours zero-filled by src-size 0 (no request at all).
+// The producer warps must be lean: a first version with ~20 SASS instructions per copy was bound by their issue latency
+// (profiles/r01_conv_variants.md).  One CTA owns T adjacent tiles: a stage holds T gathered sub-tiles and ONE weight slice
+// (for cout_p >= 64 the slice is as many L2 bytes as a tile's rows), warp (g, t) gathers tile t of items g, g+P, ..., the MMA
+// thread issues T accumulations (TMEM columns t*cout_p) against the same B descriptor, and a tile that does not use an offset
+// skips both its gather and its MMAs.  Per-element accumulation order is k_conv_tc's (ascending offset, chunk): same bits.
+// (A hybrid with tile 0 gathered by TMA gather4 and tile 1 by the LSU was measured and is slower than LSU-only: 0.68 vs 0.53 ms
+// on the 27x128x64 layer; the gather4 row rate, ~4 cycles per row per SM, paces the pair.)
 template <int T>
 __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p) {
     constexpr int MMA_WARP = 4 * T;
@@ -558,10 +525,10 @@ extern "C" long pcg_tc_set_mt_min_tiles(long tiles) {
     return prev;
 }
 
-template <int RB, bool LSU>
+template <int RB>
 static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cudaStream_t st) {
-    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB, LSU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_tc<RB, LSU><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
+    PCG_CUDA(cudaFuncSetAttribute(k_conv_tc<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_conv_tc<RB><<<(unsigned)cdiv(p.n_out, TC_ROWS), 160, smem, st>>>(tm, p);
     PCG_LAUNCHED();
     return 0;
 }
@@ -605,14 +572,16 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     cudaStream_t st = as_stream(stream);
     if (rb == 128 && (p.cout_p & 31) == 0 && tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma"))) {
         // 128-byte operand rows: LSU-gather kernel.  Static shape rule (measured with tools/bench_conv.py, profiles/r01_conv_variants.md):
+        //   at most one wave of tiles                        one tile per CTA, one CTA per SM, deepest ring
         //   wide outputs (weight slice >= 24 KiB per stage)  two tiles per CTA, one CTA per SM, deep ring
         //   large grids                                      two tiles per CTA, two CTAs per SM (16 producer warps per SM)
-        //   small grids                                      one tile per CTA, three CTAs per SM (most independent pipelines)
+        //   other grids                                      one tile per CTA, three CTAs per SM (most independent pipelines)
         static const int mt_t = getenv("PCG_TC_MT_T") ? atoi(getenv("PCG_TC_MT_T")) : 0;          // tuning knobs: force T / the smem budget
         static const int mt_kb = getenv("PCG_TC_MT_SMEM_KB") ? atoi(getenv("PCG_TC_MT_SMEM_KB")) : 0;
         const long tiles = cdiv(n_out, TC_ROWS);
         int T, kb;
-        if (p.cout_p > 128) { T = 2; kb = 200; }
+        if (tiles <= PCG_SMS) { T = 1; kb = 200; }                                  // at most one CTA per SM: deepest ring
+        else if (p.cout_p > 128) { T = tiles >= 2 * PCG_SMS ? 2 : 1; kb = 200; }
         else if (tiles >= tc_mt_min_tiles()) { T = 2; kb = 104; }
         else { T = 1; kb = 70; }
         if (mt_t == 1 || mt_t == 2) T = mt_t;
@@ -646,9 +615,7 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     p.stages = stages;
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
-    static const bool lsu = getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "lsu");   // A/B knob (tools/bench_conv.py)
-    if (rb == 32) return launch_tc<32, false>(tm, p, smem, st);
-    if (rb == 64) return launch_tc<64, false>(tm, p, smem, st);
-    if (lsu) return launch_tc<128, true>(tm, p, smem, st);
-    return launch_tc<128, false>(tm, p, smem, st);
+    if (rb == 32) return launch_tc<32>(tm, p, smem, st);
+    if (rb == 64) return launch_tc<64>(tm, p, smem, st);
+    return launch_tc<128>(tm, p, smem, st);
 }

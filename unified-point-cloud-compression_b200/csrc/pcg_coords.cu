@@ -442,6 +442,53 @@ extern "C" int pcg_prune_rows(const int32_t *coords, const float *feats, long n,
     return 0;
 }
 
+// Source rows of the kept entries of a mask, ascending (the index form of pcg_prune_rows): lets the caller compose the
+// prune with a re-ordering of the survivors and move the feature rows once (pcg_gather_rows) instead of twice.
+struct EmitIndex {
+    int32_t *rows;
+    __device__ void operator()(long i, int rank) const { rows[rank] = (int)i; }
+};
+extern "C" int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
+                                void *stream) {
+    PcgScratch s;
+    PCG_CHECK_ARG(pcg_carve_scratch(scratch, scratch_bytes, n, s), "pcg_mask_to_rows: scratch too small (%zu < %zu)", scratch_bytes,
+                  pcg_compact_scratch_bytes(n));
+    return pcg_compact(n, FlagMask{mask}, EmitIndex{out_rows}, d_n_out, s, as_stream(stream));
+}
+
+// out[r] = src[rows[r]] for r < n_rows: coordinate rows (int32 x 4, src_coords/out_coords optional) and fp32 feature rows of c
+// channels (optional), one warp per row.
+__global__ void k_gather_rows2(const int32_t *__restrict__ src_coords, const float *__restrict__ feats, int c,
+                               const int32_t *__restrict__ rows, long n, int32_t *__restrict__ out_coords, float *__restrict__ out) {
+    long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    long nwarps = ((long)gridDim.x * blockDim.x) >> 5;
+    for (long r = warp; r < n; r += nwarps) {
+        const long sr = rows[r];
+        if (src_coords && lane == 0) reinterpret_cast<int4 *>(out_coords)[r] = pcg_ld_coord(src_coords, sr);
+        if (feats) {
+            const float *src = feats + sr * c;
+            float *dst = out + r * c;
+            if ((c & 3) == 0) {
+                for (int j = lane; j < (c >> 2); j += 32)
+                    reinterpret_cast<float4 *>(dst)[j] = __ldg(reinterpret_cast<const float4 *>(src) + j);
+            } else {
+                for (int j = lane; j < c; j += 32) dst[j] = __ldg(src + j);
+            }
+        }
+    }
+}
+extern "C" int pcg_gather_rows(const int32_t *coords, const float *feats, int c, const int32_t *rows, long n_rows,
+                               int32_t *out_coords, float *out_feats, void *stream) {
+    PCG_CHECK_ARG(n_rows >= 0 && (feats == nullptr || c >= 1), "pcg_gather_rows: n_rows=%ld c=%d", n_rows, c);
+    if (n_rows == 0 || (!coords && !feats)) return 0;
+    long blocks = cdiv(n_rows * 32, 256);
+    if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+    k_gather_rows2<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(coords, feats, c, rows, n_rows, out_coords, out_feats);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------- lexsort
 __device__ __forceinline__ uint64_t spread3(uint32_t v) {   // 16 bits -> every third bit of 48
     uint64_t x = v & 0xFFFFu;

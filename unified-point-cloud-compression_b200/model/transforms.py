@@ -101,12 +101,16 @@ class SparseSynthesisTransform(nn.Module):
         """Rows under `mask`.  reorder=True additionally puts the survivors in Z-order (row order is free in ME
         semantics): they are the parents of the next generative level, whose candidates inherit the parents'
         order class by class -- without it spatial coherence (= L2 hit rate of every gather) decays level by level."""
+        do_reorder = reorder and not os.environ.get("PCG_NO_REORDER")
         if torch.is_grad_enabled() and x.F.requires_grad:
             oc, _ = so.prune_rows(x.C, None, mask, n_keep=n_keep)
             of = x.F[mask]                              # differentiable row gather (training)
+        elif do_reorder and n_keep is not None:
+            oc, of = so.prune_rows_reordered(x.C, x.F, mask, n_keep)      # prune + Z-order in one pass over the feature rows
+            return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
         else:
             oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
-        if reorder and oc.shape[0] > 1 and not os.environ.get("PCG_NO_REORDER"):
+        if do_reorder and oc.shape[0] > 1:
             perm = so.sort_rows(oc, morton=True)
             oc, of = oc[perm].contiguous(), of[perm].contiguous()
         return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))

@@ -599,19 +599,19 @@ def topk_mask(logits, coords, k_per_batch):
     n = lg.shape[0]
     mask = torch.zeros(n, dtype=torch.uint8, device=lg.device)
     if n == 0:
-        return mask.bool()
+        return mask.view(torch.bool)
     lib = _lib.load()
     ws = scratch(lib.pcg_scratch_bytes(n), lg.device)
     for b, k in enumerate(k_per_batch):
         call("pcg_topk_mask", ptr(lg), ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
-    return mask.bool()
+    return mask.view(torch.bool)          # the kernel writes 0 / 1
 
 
 def prune_rows(coords, feats, mask, n_keep=None):
     """Order-preserving compaction of (coords, feats) under a bool mask (ME.MinkowskiPruning)."""
     n = mask.shape[0]
     dev = mask.device
-    m8 = mask.to(torch.uint8).contiguous()
+    m8 = (mask.view(torch.uint8) if mask.dtype == torch.bool else mask.to(torch.uint8)).contiguous()
     lib = _lib.load()
     ws = scratch(lib.pcg_scratch_bytes(max(n, 1)) + 4 * max(n, 1), dev)
     cnt = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -622,6 +622,37 @@ def prune_rows(coords, feats, mask, n_keep=None):
     call("pcg_prune_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, n,
          feats.shape[1] if feats is not None else 0, ptr(m8), ptr(oc), ptr(of), ptr(cnt), ptr(ws), ws.numel(), stream())
     return oc, of
+
+
+def gather_rows(coords, feats, rows):
+    """(coords[rows], feats[rows]) for an int32 row list; either input may be None."""
+    n = int(rows.shape[0])
+    dev = rows.device
+    oc = torch.empty((n, 4), dtype=torch.int32, device=dev) if coords is not None else None
+    of = torch.empty((n, feats.shape[1]), dtype=torch.float32, device=dev) if feats is not None else None
+    call("pcg_gather_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, feats.shape[1] if feats is not None else 0,
+         ptr(rows), n, ptr(oc), ptr(of), stream())
+    return oc, of
+
+
+def prune_rows_reordered(coords, feats, mask, n_keep):
+    """Rows under `mask` in (batch, Z-order) order: the prune (ME.MinkowskiPruning) composed with the Z-order re-sort of the
+    survivors.  The feature rows move once: kept-row list -> Morton permutation of the kept coordinates -> one gather."""
+    n = mask.shape[0]
+    dev = mask.device
+    m8 = mask.view(torch.uint8) if mask.dtype == torch.bool else mask.to(torch.uint8)
+    lib = _lib.load()
+    n_keep = int(n_keep)
+    rows = torch.empty(max(n_keep, 1), dtype=torch.int32, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = scratch(lib.pcg_scratch_bytes(max(n, 1)), dev)
+    call("pcg_mask_to_rows", ptr(m8.contiguous()), n, ptr(rows), ptr(cnt), ptr(ws), ws.numel(), stream())
+    rows = rows[:n_keep]
+    oc, _ = gather_rows(coords, None, rows)
+    if n_keep > 1:
+        perm = sort_rows_i32(oc, morton=True)
+        rows = torch.index_select(rows, 0, perm)
+    return gather_rows(coords, feats, rows)
 
 
 def features_at(feats, cset, query):
