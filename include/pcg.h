@@ -249,6 +249,17 @@ int pcg_gc_dequant_offsets(const float *q, const float *scales_hat, const float 
                            const float *rescale, long n, int c, long sn, long sc, long gsn, long gsc,
                            const float *mlp, float scale_bound, float *y_hat, void *stream);
 
+/* ---- PSNR metric: nearest-neighbour association of two voxel clouds (metrics/metric.py:36-43,107-166) ----
+ * keys/vals/cap: coordinate hash of cloud B (pcg_hash_build).  For every row of a_coords (int32 (b,x,y,z)) finds the
+ * nearest row of B by probing growing Chebyshev shells (at most max_radius): nn_index (smallest row among equidistant
+ * neighbours), nn_d2 (integer squared distance), and -- when yuv_sqerr, a_colors and b_colors (fp32 rgb in [0,1], 3 per
+ * row) are given -- the per-point squared BT.709 YUV error after the reference's 8-bit rounding, with the colours of
+ * equidistant neighbours averaged as metric.py:127-146 does (first neighbour counted twice, five nearest at most).
+ * *d_status bit 0: some point had no neighbour within max_radius (its nn_index / nn_d2 are -1). */
+int pcg_nn_search(const uint64_t *keys, const int32_t *vals, long cap, const float *b_colors, const int32_t *a_coords,
+                  const float *a_colors, long na, int max_radius, int32_t *nn_index, int32_t *nn_d2, float *yuv_sqerr,
+                  int32_t *d_status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

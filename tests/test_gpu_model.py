@@ -142,6 +142,12 @@ def test_decoded_psnr_matches_oracle(pkg, dev, mode):
     y = abs(got["sym_y_psnr"] - ref["sym_y_psnr"])
     print(f"[psnr {mode}] D1 {got['sym_psnr_mse']:.3f} vs {ref['sym_psnr_mse']:.3f} dB, Y {got['sym_y_psnr']:.3f} vs {ref['sym_y_psnr']:.3f} dB")
     assert d1 <= 0.05 and y <= 0.05, f"D1-PSNR delta {d1:.3f} dB, Y-PSNR delta {y:.3f} dB"
+    # the same gate evaluated by the GPU metric (pcg_nn_search): identical D1, Y within the gate's tolerance
+    import importlib
+    mm = importlib.import_module(pkg.__name__ + ".metrics")
+    g = mm.pointcloud_metrics(torch.from_numpy(np.asarray(src, np.float64)).to(dev), torch.from_numpy(np.asarray(rec, np.float64)).to(dev),
+                              resolution=63)
+    assert abs(g["sym_psnr_mse"] - got["sym_psnr_mse"]) < 1e-9 and abs(g["sym_y_psnr"] - got["sym_y_psnr"]) <= 0.05
 
 
 @pytest.mark.parametrize("shepard", [False, True])

@@ -22,6 +22,7 @@ order = so.sort_rows(C, morton=True)
 cs1 = so.CoordSet(C[order].contiguous(), 1)
 cs2 = cs1.strided(2)
 cs4 = cs2.strided(2)
+cs8 = cs4.strided(2)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 
@@ -61,4 +62,7 @@ with torch.no_grad():
     run("27x192x256 stride-2 set (214k)", cs2, cs2, 192, 256, 3)
     run("125x128x128 s2 -> s4 (strided)", cs2, cs4, 128, 128, 5)
     run("125x128x128 stride-4 set (54k)", cs4, cs4, 128, 128, 5)
+    run("125x128x128 s4 -> s8 (strided)", cs4, cs8, 128, 128, 5)
+    run("125x128x128 stride-8 set (14k)", cs8, cs8, 128, 128, 5)
+    run("27x192x192 stride-8 set (14k)", cs8, cs8, 192, 192, 3)
     run("27x32x16   stride-1 set (818k)", cs1, cs1, 32, 16, 3)

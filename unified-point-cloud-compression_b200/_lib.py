@@ -55,6 +55,7 @@ _PROTOS = {
     "pcg_gdn_fwd": (_I, [_P, _L, _I, _P, _P, _I, _P, _P]),
     "pcg_topk_mask": (_I, [_P, _P, _L, _I, _L, _P, _P, _SZ, _P]),
     "pcg_prune_rows": (_I, [_P, _P, _L, _I, _P, _P, _P, _P, _P, _SZ, _P]),
+    "pcg_nn_search": (_I, [_P, _P, _L, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P]),
     "pcg_mask_to_rows": (_I, [_P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_gather_rows": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
     "pcg_features_at": (_I, [_P, _P, _L, _P, _I, _I, _P, _L, _P, _P]),
