@@ -56,8 +56,10 @@ def test_nearest_neighbours_match_brute_force(pkg, dev):
 
 def test_unique_neighbour_colours_are_exact_and_identical_clouds_are_lossless(pkg, dev):
     mm = metrics_mod(pkg)
-    src = np.array([[0, 0, 0, 0.2, 0.4, 0.6], [4, 0, 0, 0.8, 0.1, 0.3]], dtype=np.float64)
-    rec = np.array([[0, 0, 1, 0.2, 0.4, 0.6], [4, 1, 0, 0.8, 0.1, 0.3], [9, 9, 9, 0.0, 0.0, 0.0]], dtype=np.float64)
+    # colours away from the x.5 / 255 rounding points: the product keeps colours in fp32 (they are k / 255 in practice), the
+    # oracle in fp64, and 0.1 * 255 = 25.5 rounds differently in the two
+    src = np.array([[0, 0, 0, 0.2, 0.4, 0.6], [4, 0, 0, 0.8, 0.12, 0.31]], dtype=np.float64)
+    rec = np.array([[0, 0, 1, 0.2, 0.4, 0.6], [4, 1, 0, 0.8, 0.12, 0.31], [9, 9, 9, 0.0, 0.0, 0.0]], dtype=np.float64)
     ref = metric_ref.pointcloud_metrics(src, rec, resolution=15)
     got = mm.pointcloud_metrics(torch.from_numpy(src).to(dev), torch.from_numpy(rec).to(dev), resolution=15)
     for k in ("AB_mse", "BA_mse", "AB_y_mse", "BA_y_mse", "BA_u_mse", "BA_v_mse", "sym_psnr_mse"):

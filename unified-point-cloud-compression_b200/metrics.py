@@ -4,6 +4,7 @@ The reference associates the two clouds with per-point KD-tree queries in Python
 launch of `pcg_nn_search` (hash-probe shell search, csrc/pcg_metric.cu), which also evaluates the per-point colour error
 terms (8-bit rounding, BT.709 YUV, equidistant-neighbour colour averaging, :127-166).  Only the final means / maxima /
 log10 are taken with torch reductions in float64.  Same result keys as the reference (`AB_*`, `BA_*`, `sym_*`).
+Colours are carried in fp32 (the codec's own precision; k/255 inputs round to the same 8-bit value as in fp64).
 """
 import math
 
