@@ -214,6 +214,100 @@ __global__ void __launch_bounds__(256) k_gdn_mma(const float *__restrict__ x, lo
     }
 }
 
+// Same op on mma.sync.m16n8k16 with the bf16x3 split (x = x_hi + x_lo, gamma = g_hi + g_lo in bf16; x_lo*g_hi + x_hi*g_lo +
+// x_hi*g_hi, fp32 accumulate: ~2^-16 relative per term, still far inside fp32-conv noise).  Per 16 reduction channels this is
+// 3 MMAs + one 16-byte fragment load, against 6 MMAs + 12 conversion instructions for 3xTF32 whose gamma split was redone in
+// the inner loop.  Lane (g, t) owns channels [32q+8t, +8) of rows g and g+8; slab s of the pair takes its channels 4s..4s+3
+// as k-slots {2t, 2t+1, 2t+8, 2t+9}; the gamma fragments in shared memory follow the same permutation.
+__device__ __forceinline__ void mma_16816_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void split_bf16x2(float v0, float v1, uint32_t &hi, uint32_t &lo) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v0, v1);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(v0 - __low2float(h), v1 - __high2float(h));
+    hi = *reinterpret_cast<const uint32_t *>(&h);
+    lo = *reinterpret_cast<const uint32_t *>(&l);
+}
+
+template <int C>
+__global__ void __launch_bounds__(256) k_gdn_mma16(const float *__restrict__ x, long n, const float *__restrict__ beta,
+                                                   const float *__restrict__ gamma, int inverse, float *__restrict__ out) {
+    constexpr int Q = C / 32, NT = C / 8;
+    extern __shared__ uint4 bq_s[];                 // [Q][2][NT][32]: {b0_hi, b1_hi, b0_lo, b1_lo} of output channel nt*8+g
+    for (int i = threadIdx.x; i < Q * 2 * NT * 32; i += blockDim.x) {
+        const int lane = i & 31, nt = (i >> 5) % NT, sl = ((i >> 5) / NT) & 1, q = (i >> 5) / (NT * 2);
+        const int g = lane >> 2, t = lane & 3;
+        const float *gr = gamma + (long)(nt * 8 + g) * C + 32 * q + 8 * t + 4 * sl;
+        uint4 v;
+        split_bf16x2(__ldg(gr), __ldg(gr + 1), v.x, v.z);
+        split_bf16x2(__ldg(gr + 2), __ldg(gr + 3), v.y, v.w);
+        bq_s[i] = v;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    for (long tile = blockIdx.x; tile * 128 < n; tile += gridDim.x) {
+        const long row0 = (tile * 8 + (threadIdx.x >> 5)) * 16;
+        if (row0 >= n) continue;
+        const long r0 = row0 + g, r1 = row0 + g + 8;
+        const bool ok0 = r0 < n, ok1 = r1 < n;
+        float acc[NT][4];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[nt][c] = 0.f;
+#pragma unroll 1
+        for (int q = 0; q < Q; ++q) {
+#pragma unroll
+            for (int sl = 0; sl < 2; ++sl) {
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 u0 = ok0 ? __ldg(reinterpret_cast<const float4 *>(x + r0 * C + 32 * q + 8 * t) + sl) : z;
+                const float4 u1 = ok1 ? __ldg(reinterpret_cast<const float4 *>(x + r1 * C + 32 * q + 8 * t) + sl) : z;
+                uint32_t ah[4], al[4];      // a0 = (row g, slots 2t,2t+1), a1 = (row g+8, same), a2 = (row g, slots 2t+8,2t+9), a3 = (row g+8, same)
+                split_bf16x2(fabsf(u0.x), fabsf(u0.y), ah[0], al[0]);
+                split_bf16x2(fabsf(u1.x), fabsf(u1.y), ah[1], al[1]);
+                split_bf16x2(fabsf(u0.z), fabsf(u0.w), ah[2], al[2]);
+                split_bf16x2(fabsf(u1.z), fabsf(u1.w), ah[3], al[3]);
+                const uint4 *bq = bq_s + ((q * 2 + sl) * NT) * 32 + lane;
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const uint4 b = bq[nt * 32];
+                    mma_16816_bf16(acc[nt], al[0], al[1], al[2], al[3], b.x, b.y);
+                    mma_16816_bf16(acc[nt], ah[0], ah[1], ah[2], ah[3], b.z, b.w);
+                    mma_16816_bf16(acc[nt], ah[0], ah[1], ah[2], ah[3], b.x, b.y);
+                }
+            }
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int col = nt * 8 + 2 * t;
+            const float2 bt = __ldg(reinterpret_cast<const float2 *>(beta + col));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const long r = h ? r1 : r0;
+                if (!(h ? ok1 : ok0)) continue;
+                const float2 xv = __ldg(reinterpret_cast<const float2 *>(x + r * C + col));
+                const float n0 = acc[nt][2 * h] + bt.x, n1 = acc[nt][2 * h + 1] + bt.y;
+                float2 o;
+                o.x = inverse ? xv.x * n0 : xv.x * (1.0f / n0);
+                o.y = inverse ? xv.y * n1 : xv.y * (1.0f / n1);
+                *reinterpret_cast<float2 *>(out + r * C + col) = o;
+            }
+        }
+    }
+}
+
+template <int C>
+static int launch_gdn_mma16(const float *x, long n, const float *beta, const float *gamma, int inverse, float *out, cudaStream_t st) {
+    const size_t smem = (size_t)(C / 32) * 2 * (C / 8) * 32 * sizeof(uint4);
+    PCG_CUDA(cudaFuncSetAttribute(k_gdn_mma16<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long tiles = cdiv(n, 128);
+    k_gdn_mma16<C><<<(unsigned)(tiles < 2 * PCG_SMS ? tiles : 2 * PCG_SMS), 256, smem, st>>>(x, n, beta, gamma, inverse, out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 template <int C>
 static int launch_gdn_mma(const float *x, long n, const float *beta, const float *gamma, int inverse, float *out, cudaStream_t st) {
     const size_t smem = (size_t)(C / 32) * 4 * (C / 8) * 32 * sizeof(float2);
@@ -229,6 +323,12 @@ extern "C" int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, con
     if (n <= 0) return 0;
     cudaStream_t st = as_stream(stream);
     const bool aligned = (((uintptr_t)x | (uintptr_t)out) & 15) == 0 && ((uintptr_t)beta & 7) == 0;
+    static const bool tf32 = getenv("PCG_GDN") && !strcmp(getenv("PCG_GDN"), "tf32");     // A/B knob: the 3xTF32 version
+    if (aligned && !tf32) {
+        if (c == 128) return launch_gdn_mma16<128>(x, n, beta, gamma, inverse, out, st);
+        if (c == 64) return launch_gdn_mma16<64>(x, n, beta, gamma, inverse, out, st);
+        if (c == 32) return launch_gdn_mma16<32>(x, n, beta, gamma, inverse, out, st);
+    }
     if (aligned && c == 128) return launch_gdn_mma<128>(x, n, beta, gamma, inverse, out, st);
     if (aligned && c == 64) return launch_gdn_mma<64>(x, n, beta, gamma, inverse, out, st);
     if (aligned && c == 32) return launch_gdn_mma<32>(x, n, beta, gamma, inverse, out, st);
