@@ -135,6 +135,7 @@ def main():
     ap.add_argument("--workload", default="frame10", choices=["frame10", "block128", "frame11"])
     ap.add_argument("--conv-mode", default="auto", choices=["auto", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=2, help="frames in flight per GPU (host threads x CUDA streams); 1 = single stream")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: anything libraries print there (e.g. NCCL's version banner) goes to stderr
     sys.stdout.flush()
@@ -148,9 +149,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": f"CVPR_inverse_scaling {args.workload}: one synthetic surface-sampled frame per rank per step, "
+    config = {"workload": f"CVPR_inverse_scaling {args.workload}: {max(1, args.in_flight)} synthetic surface-sampled frame(s) per rank per step, "
                           "compress+decompress, random-init weights, q=(0.5,0.5)",
-              "sharding": f"{world} rank(s), one frame each, no collective"}
+              "sharding": f"{world} rank(s), independent frames on each, no collective"}
 
     if args.impl == "reference":
         if rank != 0:
@@ -184,43 +185,49 @@ def main():
     net.update()
     q = torch.tensor([[0.5, 0.5]], device=dev)
 
-    pts, rgb = make_frame(args.workload, seed=rank)
-    n_points = len(pts)
-    host_cloud = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).pin_memory()
-    dev_cloud = host_cloud.to(dev)
+    depth = max(1, args.in_flight)
+    # a step codes `depth` frames (one per worker stream): frame seeds rank, rank + world, ...
+    frames = [make_frame(args.workload, seed=rank + j * world) for j in range(depth)]
+    n_points = sum(len(p) for p, _ in frames)
+    host_clouds = [torch.from_numpy(np.concatenate([p.astype(np.float32), c], axis=1)).pin_memory() for p, c in frames]
+    dev_clouds = [h.to(dev) for h in host_clouds]
+    codec_mod = importlib.import_module(pkg.__name__ + ".codec")
+    pipe = codec_mod.FramePipeline(dev, depth) if depth > 1 else None
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
-    def step_resident():
+    def step_resident(j=0):
+        dev_cloud = dev_clouds[j]
         enc = net.encode_block(dev_cloud, q)
         ys = enc["y_symbols"]
         x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], q)
         return net.finalize(x_hat.C, x_hat.F)
 
-    bytes_io = {"h2d": 0, "d2h": 0}
+    io_frame = {}                                        # frame slot -> (h2d bytes, d2h bytes) of one step
 
     pinned = {}
 
-    def to_host(name, t):
+    def to_host(name, t, slot=0):
         """D2H into a persistent pinned buffer (allocated on first use), asynchronous on the current stream."""
         t = t.contiguous()
+        name = (slot, name)                              # one set of buffers per frame slot (a slot is coded by one worker at a time)
         buf = pinned.get(name)
         if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
             buf = pinned[name] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
         buf.copy_(t, non_blocking=True)
         return buf
 
-    def step_e2e():
-        x = host_cloud.to(dev, non_blocking=True)
+    def step_e2e(j=0):
+        x = host_clouds[j].to(dev, non_blocking=True)
         enc = net.encode_block(x, q)
-        host = {k: to_host(k, enc[k]) for k in ("y_points", "z_symbols", "y_symbols", "y_indexes")}
+        host = {k: to_host(k, enc[k], j) for k in ("y_points", "z_symbols", "y_symbols", "y_indexes")}
         torch.cuda.current_stream().synchronize()
         # (host range coder runs here in a deployment; excluded by the metric)
         yp, zs, ys = (host[k].to(dev, non_blocking=True) for k in ("y_points", "z_symbols", "y_symbols"))
         x_hat = net.decode_block(yp, zs, lambda idx: ys, enc["k"], q)
-        rec = to_host("rec", net.finalize(x_hat.C, x_hat.F))
+        rec = to_host("rec", net.finalize(x_hat.C, x_hat.F), j)
         torch.cuda.current_stream().synchronize()
-        bytes_io["h2d"] = x.numel() * 4 + sum(host[k].numel() * host[k].element_size() for k in ("y_points", "z_symbols", "y_symbols"))
-        bytes_io["d2h"] = sum(v.numel() * v.element_size() for v in host.values()) + rec.numel() * rec.element_size()
+        io_frame[j] = (x.numel() * 4 + sum(host[k].numel() * host[k].element_size() for k in ("y_points", "z_symbols", "y_symbols")),
+                       sum(v.numel() * v.element_size() for v in host.values()) + rec.numel() * rec.element_size())
         return rec
 
     def barrier():
@@ -228,7 +235,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, steps, use_pipe=True):
         total = 0.0
         per_step = []
         host_ms = []
@@ -237,7 +244,10 @@ def main():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             t0 = time.perf_counter()
-            fn()
+            if pipe is None or not use_pipe:
+                fn()
+            else:
+                pipe.map(fn, range(depth), after=e0)             # `depth` frames, one per worker stream; this stream waits for all
             host_ms.append(1e3 * (time.perf_counter() - t0))     # host enqueue time (includes the step's own syncs)
             e1.record()
             flush[:1].fill_(2)                               # 1-block marker launch: end of the step in an ncu launch list
@@ -250,8 +260,13 @@ def main():
 
     with torch.no_grad():
         for _ in range(max(args.warmup, 3)):
-            step_resident()
+            for j in range(depth):
+                step_resident(j)
         barrier()
+        if pipe is not None:                                     # warm the worker streams too (scratch, allocator pools)
+            for _ in range(2):
+                pipe.map(step_resident, range(depth))
+            barrier()
         clocks = ClockSampler(local_rank)
         l0 = pkg._lib.launch_count()
         t_res = timed(step_resident, args.steps)
@@ -259,9 +274,15 @@ def main():
         barrier()
         clk = clocks.stop()
         for _ in range(3):
-            step_e2e()
+            for j in range(depth):
+                step_e2e(j)
+        if pipe is not None:
+            pipe.map(step_e2e, range(depth))
         barrier()
         t_e2e = timed(step_e2e, args.steps)
+        # the same frame (slot 0) alone on one stream, for reference next to the frames-in-flight numbers
+        t_res1 = timed(step_resident, min(args.steps, 5), use_pipe=False) / min(args.steps, 5) if pipe is not None else None
+        t_e2e1 = timed(step_e2e, min(args.steps, 5), use_pipe=False) / min(args.steps, 5) if pipe is not None else None
         barrier()
         # roofline pass: the same step with per-launch CUDA events around every convolution kernel
         so.profiler = so.ConvProfiler()
@@ -286,6 +307,8 @@ def main():
     ms_res, ms_e2e = reduce_max(t_res) / args.steps, reduce_max(t_e2e) / args.steps
     total_points = reduce_sum(n_points)
     if rank != 0:
+        if pipe is not None:
+            pipe.close()
         if world > 1:
             dist.destroy_process_group()
         return
@@ -317,7 +340,8 @@ def main():
                 "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops"],
                 "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu, profiles/r01_ncu_full_v5.md)",
                 "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
-                "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms / ms_res if ms_res else None,
+                "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * depth / ms_res if ms_res else None,
+                "per": "one frame (the roofline pass codes a single frame on one stream)",
                 "algorithmic_gflop_per_step": tc_flops / 1e9,
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},
                 "hbm_bound_kernels": {"gent_reduce (k_cells_reduce)": hbm("gent_reduce"), "conv_narrow (k_conv_mma)": hbm("conv_narrow"),
@@ -326,16 +350,23 @@ def main():
     line = {"metric": METRIC, "value": total_points / (ms_res * 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
-            "config": dict(config, points_per_frame=n_points, l2="512 MiB flush buffer written between timed steps",
-                           conv_mode=args.conv_mode),
+            "config": dict(config, points_per_step=n_points, frames_per_step=depth,
+                           in_flight=f"{depth} frame(s) in flight per GPU: {depth} host thread(s) x CUDA stream(s) (codec.FramePipeline)",
+                           l2="512 MiB flush buffer written between timed steps", conv_mode=args.conv_mode),
             "clocks": clk,
             "e2e": {"value": total_points / (ms_e2e * 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": bytes_io["h2d"], "d2h_bytes_per_step": bytes_io["d2h"]},
+                    "h2d_bytes_per_step": sum(v[0] for v in io_frame.values()), "d2h_bytes_per_step": sum(v[1] for v in io_frame.values())},
             "gpu_launches": int(launches), "roofline": roofline}
+    if t_res1 is not None:
+        n1 = len(frames[0][0])
+        line["single_stream"] = {"note": "one frame at a time on one stream, rank 0", "ms_per_frame": t_res1, "value": n1 / (t_res1 * 1e3),
+                                 "e2e_ms_per_frame": t_e2e1, "e2e_value": n1 / (t_e2e1 * 1e3), "unit": UNIT}
     if world == 1 and not args.no_cpu_baseline:
         r = run_cpu(args.workload, 1, 0)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
     emit(line)
+    if pipe is not None:
+        pipe.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -181,3 +181,44 @@ def test_training_step_runs_and_learns(pkg, dev, shepard):
     assert not missing, f"parameters without gradient: {missing}"
     assert all(torch.isfinite(p.grad).all() for p in net.parameters() if p.grad is not None)
     assert min(losses[1:]) < losses[0], losses      # (the colour term is defined on a changing voxel set, so not monotone)
+
+
+def test_frames_in_flight_reproduce_single_stream_results(pkg, dev):
+    """codec.FramePipeline (host threads x CUDA streams, several frames in flight on one GPU): every frame's symbols,
+    coordinates and reconstruction are bit-identical to coding the frames one after the other on one stream."""
+    import importlib
+    from oracle import synth
+    from tests.helpers import model_config, spread_weights
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    codec = importlib.import_module(pkg.__name__ + ".codec")
+    torch.manual_seed(0)
+    net = model_mod.UnifiedModel(model_config(width=32))
+    spread_weights(net)
+    net = net.to(dev).eval()
+    net.update()
+    q = torch.tensor([[0.5, 0.5]], device=dev)
+    clouds = []
+    for seed in range(5):
+        pts, rgb = synth.small_cloud(seed=seed + 1, radius=9.0 + seed, centre=(20, 20, 20), n_samples=7000)
+        clouds.append(torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).to(dev))
+
+    def code(cloud):
+        enc = net.encode_block(cloud, q)
+        ys = enc["y_symbols"]
+        x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], q)
+        return enc["y_symbols"].clone(), enc["z_symbols"].clone(), enc["y_points"].clone(), net.finalize(x_hat.C, x_hat.F)
+
+    with torch.no_grad():
+        ref = [code(c) for c in clouds]
+        torch.cuda.synchronize()
+        pipe = codec.FramePipeline(dev, depth=3)
+        try:
+            for _ in range(2):
+                got = pipe.map(code, clouds)
+                torch.cuda.synchronize()
+                for a, b in zip(ref, got):
+                    assert all(torch.equal(x, y) for x, y in zip(a, b))
+            with pytest.raises(ZeroDivisionError):           # a worker's exception surfaces in the submitting thread
+                pipe.map(lambda c: 1 // 0, clouds[:1])
+        finally:
+            pipe.close()

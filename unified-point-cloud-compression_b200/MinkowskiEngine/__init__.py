@@ -141,7 +141,10 @@ class MinkowskiConvolutionBase(nn.Module):
             if self.bias is not None:
                 self.bias.uniform_(-stdv, stdv)
 
-    def forward(self, input, coordinates=None):
+    def forward(self, input, coordinates=None, _act=None):
+        # _act: activation fused into the epilogue for THIS call (passed as an argument, not kept on the module: several
+        # frames may run through the same module concurrently, codec.FramePipeline)
+        act = self.fused_activation if _act is None else _act
         if not isinstance(input, SparseTensor):
             raise TypeError("input must be a SparseTensor")
         if input.F.shape[1] != self.in_channels:
@@ -154,7 +157,7 @@ class MinkowskiConvolutionBase(nn.Module):
             if not grad and so.cells_eligible(self.kernel_size, self.stride, self.in_channels, self.out_channels):
                 # kernel 5 / stride 2: octree-cell candidate set + GEMM-first transposed convolution
                 out_set = in_set.generated_cells()
-                out = so.gen_conv_transpose_cells(input.F, in_set, out_set, self.kernel, self.bias, act=self.fused_activation,
+                out = so.gen_conv_transpose_cells(input.F, in_set, out_set, self.kernel, self.bias, act=act,
                                                   packed=self._packed_gemm, out=self.emit)
                 return SparseTensor(out, _coord_set=out_set)
             out_set = in_set.generated(self.kernel_size, self.stride)
@@ -173,10 +176,10 @@ class MinkowskiConvolutionBase(nn.Module):
         if grad:
             from ..autograd import sparse_conv_autograd
             out = sparse_conv_autograd(input.F, in_set, out_set, self.kernel, self.bias, self.kernel_size,
-                                       self.is_transpose, self.fused_activation)
+                                       self.is_transpose, act)
         else:
             out = so.sparse_conv(input.F, in_set, out_set, self.kernel, self.bias, self.kernel_size, self.is_transpose,
-                                 act=self.fused_activation, packed=self._packed, out=self.emit)
+                                 act=act, packed=self._packed, out=self.emit)
         return SparseTensor(out, _coord_set=out_set)
 
 

@@ -65,3 +65,69 @@ class StreamCodec:
             f = frames[i]() if callable(frames[i]) else frames[i]
             local[i] = keep(self.code_frame(f))
         return gather_results(local, self.world, self.rank)
+
+
+class FramePipeline:
+    """Several frames in flight on ONE GPU: `depth` host threads, each with its own CUDA stream.
+
+    Coding a frame is a chain of ~450 launches whose buffer sizes are data dependent (coordinate-set sizes come back
+    from the device: ~18 stream synchronisations per frame), so a single stream leaves the GPU idle for ~10 % of a
+    frame while the host wakes up and enqueues again.  Frames are independent (intra-only codec), so a second frame on
+    another stream fills those gaps; the ctypes calls into libpcg.so, torch's launches and `.item()` all release the
+    GIL.  Every worker owns its scratch workspace (sparse_ops.scratch is keyed by stream) and its tensors; the model
+    parameters and packed weights are read-only after warm-up.  No data-path collective, no cross-stream dependency
+    other than the optional `after` event of `submit`.
+    """
+
+    def __init__(self, device, depth=2):
+        import queue
+        import threading
+        self.device = torch.device(device)
+        self.depth = int(depth)
+        self._jobs = queue.Queue()
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.depth)]
+        self._threads = [threading.Thread(target=self._work, args=(s,), daemon=True) for s in self.streams]
+        for t in self._threads:
+            t.start()
+
+    def _work(self, stream):
+        torch.cuda.set_device(self.device)
+        with torch.cuda.stream(stream), torch.no_grad():
+            while True:
+                job = self._jobs.get()
+                if job is None:
+                    return
+                fn, args, after, fut = job
+                try:
+                    if after is not None:
+                        stream.wait_event(after)
+                    res = fn(*args)
+                    done = torch.cuda.Event()
+                    done.record(stream)
+                    fut.set_result((res, done))
+                except BaseException as e:          # surfaced by Future.result() in the submitting thread
+                    fut.set_exception(e)
+
+    def submit(self, fn, *args, after=None):
+        """Run fn(*args) on the next free worker (its stream current, no_grad).  `after`: a CUDA event the worker's
+        stream waits for first.  Returns a Future of (result, CUDA event recorded when the worker's launches end)."""
+        from concurrent.futures import Future
+        fut = Future()
+        self._jobs.put((fn, args, after, fut))
+        return fut
+
+    def map(self, fn, items, after=None):
+        """fn(item) for every item, `depth` at a time; results in order.  The calling stream waits for all of them."""
+        futs = [self.submit(fn, it, after=after) for it in items]
+        out = []
+        for f in futs:
+            res, done = f.result()
+            torch.cuda.current_stream(self.device).wait_event(done)
+            out.append(res)
+        return out
+
+    def close(self):
+        for _ in self._threads:
+            self._jobs.put(None)
+        for t in self._threads:
+            t.join()

@@ -69,11 +69,7 @@ def _run_fused(seq, x):
         m = mods[i]
         nxt = mods[i + 1] if i + 1 < len(mods) else None
         if isinstance(m, ME.MinkowskiConvolutionBase) and isinstance(nxt, ME.MinkowskiLeakyReLU):
-            m.fused_activation = so.ACT_LEAKY
-            try:
-                x = m(x)
-            finally:
-                m.fused_activation = so.ACT_NONE
+            x = m(x, _act=so.ACT_LEAKY)          # per-call argument: no module state is touched (frames may run concurrently)
             i += 2
         else:
             x = m(x)
