@@ -167,6 +167,12 @@ int pcg_gemm_bf16_grouped(const void *feats_bf16, long n, int cin, const void *w
  *   3. pcg_cells_info  -> cell_mask (existing children), cell_base (first child row), *d_n_out (number of children)
  *   4. pcg_cells_emit  -> child coordinates (cell-major, bit order) and out_cell (cell of every child)
  * The child SET equals ME's unique{p + off*ts_out : off in [-2,2]^3}; the row order is libpcg's own. */
+/* pnbr[e][cell] (27 x pnbr_pitch, -1 = absent) by scatter: one probe of the cell table per (parent, offset) pair instead of
+ * 27 probes of the parent table per cell -- same table as pcg_kernel_map(parents table, cells, 3) produces.  cell_keys /
+ * cell_vals: coordinate hash of the cells (pcg_generate_coords(ksize 3, stride 1) of the parents).  *d_status bit 0: a
+ * dilated parent position is missing from the cell table (the cells are not the 3^3 dilation of these parents). */
+int pcg_cells_parent_map(const int32_t *parent_coords, long n_par, int ts, const uint64_t *cell_keys, const int32_t *cell_vals,
+                         long cell_cap, long n_cells, int32_t *pnbr, long pnbr_pitch, int32_t *d_status, void *stream);
 size_t pcg_cells_scratch_bytes(long n_cells);
 int pcg_cells_info(const int32_t *pnbr, long pnbr_pitch, long n_cells, uint8_t *cell_mask, int32_t *cell_base,
                    int32_t *d_n_out, void *scratch, size_t scratch_bytes, void *stream);

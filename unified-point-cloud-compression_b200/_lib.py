@@ -43,6 +43,7 @@ _PROTOS = {
     "pcg_pack_weights_mma": (_I, [_P, _I, _I, _I, _P, _P]),
     "pcg_conv_fwd_mma": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
     "pcg_gemm_bf16_grouped": (_I, [_P, _L, _I, _P, _L, _P, _P]),
+    "pcg_cells_parent_map": (_I, [_P, _L, _I, _P, _P, _L, _L, _P, _L, _P, _P]),
     "pcg_cells_scratch_bytes": (_SZ, [_L]),
     "pcg_cells_info": (_I, [_P, _L, _L, _P, _P, _P, _P, _SZ, _P]),
     "pcg_cells_emit": (_I, [_P, _P, _P, _L, _I, _P, _P, _P]),

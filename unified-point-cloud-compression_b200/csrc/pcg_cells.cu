@@ -30,6 +30,43 @@ __device__ __forceinline__ uint32_t cells_valid_e(int b) {
     return m;
 }
 
+// ---------------------------------------------------------------------------- parent lists by scatter
+// pnbr[e][cell] = parent row at cell + e*ts.  The cells were generated as parent + d*ts, d in {-1,0,1}^3, so every
+// (parent, d) pair names exactly one cell: one probe of the CELL table per pair (27 * n_parents probes, all hits) and a
+// scatter into pnbr[-d][cell], instead of 27 probes per cell of the parent table (~6.7x more probes, mostly misses that
+// walk a probe chain to its end).  Distinct (parent, d) pairs write distinct entries: no race, order free.
+__global__ void k_cells_parent_scatter(const int32_t *__restrict__ parent_coords, long n_par, int ts, const uint64_t *__restrict__ ckeys,
+                                       const int32_t *__restrict__ cvals, uint64_t cmask, int32_t *__restrict__ pnbr, long pitch,
+                                       int32_t *__restrict__ d_status) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_par * 27) return;
+    const long p = i / 27;
+    const int d = (int)(i - p * 27);
+    const int dx = d % 3 - 1, dy = (d / 3) % 3 - 1, dz = d / 9 - 1;
+    const int4 c = pcg_ld_coord(parent_coords, p);
+    const int x = c.y + dx * ts, y = c.z + dy * ts, z = c.w + dz * ts;
+    if (!pcg_in_range(c.x, x, y, z)) return;
+    const int cell = pcg_table_find(ckeys, cvals, cmask, pcg_pack(c.x, x, y, z));
+    if (cell < 0) { atomicOr(d_status, 1); return; }       // the cell set is not the 3^3 dilation of these parents
+    pnbr[(long)(26 - d) * pitch + cell] = (int)p;
+}
+
+extern "C" int pcg_cells_parent_map(const int32_t *parent_coords, long n_par, int ts, const uint64_t *cell_keys,
+                                    const int32_t *cell_vals, long cell_cap, long n_cells, int32_t *pnbr, long pnbr_pitch,
+                                    int32_t *d_status, void *stream) {
+    PCG_CHECK_ARG(cell_cap > 0 && (cell_cap & (cell_cap - 1)) == 0, "pcg_cells_parent_map: cell_cap=%ld must be a power of two", cell_cap);
+    PCG_CHECK_ARG(pnbr_pitch >= n_cells && ts >= 1, "pcg_cells_parent_map: pitch=%ld n_cells=%ld ts=%d", pnbr_pitch, n_cells, ts);
+    PCG_CHECK_ARG(n_par * 27 < 2147483647L, "pcg_cells_parent_map: n_par=%ld too large", n_par);
+    cudaStream_t st = as_stream(stream);
+    PCG_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    PCG_CUDA(cudaMemsetAsync(pnbr, 0xFF, (size_t)27 * pnbr_pitch * sizeof(int32_t), st));      // -1 everywhere
+    if (n_par <= 0 || n_cells <= 0) return 0;
+    k_cells_parent_scatter<<<(unsigned)cdiv(n_par * 27, 256), 256, 0, st>>>(parent_coords, n_par, ts, cell_keys, cell_vals,
+                                                                           (uint64_t)cell_cap - 1, pnbr, pnbr_pitch, d_status);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------- cell info
 // occupancy bits of the 27 parent neighbours -> 8-bit child mask + child count
 __global__ void k_cells_mask(const int32_t *__restrict__ pnbr, long pitch, long n_cells, uint8_t *__restrict__ cell_mask,

@@ -150,13 +150,20 @@ class CoordSet:
             dev = self.coords.device
             lib = _lib.load()
             cells = self.generated(3, 1, guess_per_row=14)                # parents dilated by {-1,0,1}^3 * ts
-            pnbr, _ = self.kernel_map(cells, 3, False)                    # pnbr[e][cell] = parent row at cell + e*ts
+            # pnbr[e][cell] = parent row at cell + e*ts, by scatter from the (parent, offset) pairs that generated the cells
+            ckeys, cvals, ccap = cells.table()
+            pitch = lib.pcg_nbr_pitch(cells.n)
+            pnbr = torch.empty((27, pitch), dtype=torch.int32, device=dev)
+            cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+            call("pcg_cells_parent_map", ptr(self.coords), self.n, self.ts, ptr(ckeys), ptr(cvals), ccap, cells.n, ptr(pnbr), pitch,
+                 ptr(cnt[1:2]), stream())
             mask = torch.empty(max(cells.n, 1), dtype=torch.uint8, device=dev)
             base = torch.empty(max(cells.n, 1), dtype=torch.int32, device=dev)
-            cnt = torch.zeros(1, dtype=torch.int32, device=dev)
             ws = scratch(lib.pcg_cells_scratch_bytes(max(cells.n, 1)), dev)
-            call("pcg_cells_info", ptr(pnbr), pnbr.shape[1], cells.n, ptr(mask), ptr(base), ptr(cnt), ptr(ws), ws.numel(), stream())
-            n_out = int(cnt.item())
+            call("pcg_cells_info", ptr(pnbr), pnbr.shape[1], cells.n, ptr(mask), ptr(base), ptr(cnt[0:1]), ptr(ws), ws.numel(), stream())
+            n_out, status = (int(v) for v in cnt.tolist())
+            if status:
+                raise RuntimeError("pcg_cells_parent_map: a dilated parent position is missing from the cell table")
             out = torch.empty((n_out, 4), dtype=torch.int32, device=dev)
             out_cell = torch.empty(max(n_out, 1), dtype=torch.int32, device=dev)
             call("pcg_cells_emit", ptr(cells.coords), ptr(mask), ptr(base), cells.n, self.ts // 2, ptr(out), ptr(out_cell), stream())
