@@ -13,6 +13,8 @@
 // table of all children.  Rows come out cell-major: siblings are adjacent and neighbouring cells are near.
 #include <cub/device/device_scan.cuh>
 
+#include <stdlib.h>
+
 #include "pcg_common.cuh"
 
 // valid-parent mask over the 27 e-indices (bit i = ex+1 + 3(ey+1) + 9(ez+1)) for child bit pattern b
@@ -239,67 +241,84 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
     constexpr int CPW = 32 / LANES;                 // child slots per warp
     constexpr int WPC = 8 / CPW;                    // warps per cell
     const int lane = threadIdx.x & 31;
-    const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long cell = gw / WPC;
-    if (cell >= n_cells) return;                    // warp-uniform
-    const int b = (int)(gw % WPC) * CPW + lane / LANES;
+    const long n_units = n_cells * WPC;             // one unit = the CPW child slots of one cell handled by one warp
+    const long n_warps = ((long)gridDim.x * blockDim.x) >> 5;
+    long unit = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (unit >= n_units) return;                    // warp-uniform
     const int part = lane % LANES;
-    const int bx = b & 1, by = (b >> 1) & 1, bz = (b >> 2) & 1;
-    const int my_prow = lane < 27 ? __ldg(pnbr + (long)lane * pitch + cell) : -1;
-    uint32_t present = __ballot_sync(0xffffffffu, my_prow >= 0);
-    const uint32_t cmask = cell_mask[cell];
-    const bool exists = (cmask >> b) & 1u;
-    const uint32_t reach = exists ? cells_valid_e(b) : 0u;      // parents e that reach child b
     const long t_row = (long)125 * cout;
-    float acc[8];
+    // Grid-stride over units with the NEXT unit's parent row / child mask / row base requested before the current unit's rows
+    // of T: each unit is a chain of two dependent global loads (parent list -> T rows) with few bytes in flight per warp, so the
+    // first link of unit i+1 overlaps the second link of unit i.
+    long cell = unit / WPC;
+    int my_prow = lane < 27 ? __ldg(pnbr + (long)lane * pitch + cell) : -1;
+    uint32_t cmask = cell_mask[cell];
+    int cbase = __ldg(cell_base + cell);
+    for (; unit < n_units; unit += n_warps) {
+        const long nunit = unit + n_warps;
+        const bool has_next = nunit < n_units;
+        const long ncell = has_next ? nunit / WPC : cell;
+        const int nprow = (has_next && lane < 27) ? __ldg(pnbr + (long)lane * pitch + ncell) : -1;
+        const uint32_t ncmask = has_next ? cell_mask[ncell] : 0u;
+        const int ncbase = has_next ? __ldg(cell_base + ncell) : 0;
+
+        const int b = (int)(unit % WPC) * CPW + lane / LANES;
+        const int bx = b & 1, by = (b >> 1) & 1, bz = (b >> 2) & 1;
+        uint32_t present = __ballot_sync(0xffffffffu, my_prow >= 0);
+        const bool exists = (cmask >> b) & 1u;
+        const uint32_t reach = exists ? cells_valid_e(b) : 0u;      // parents e that reach child b
+        float acc[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    while (present) {
-        int e[4], pr[4];
-        uint4 v[4];
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        while (present) {
+            int e[4], pr[4];
+            uint4 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            e[u] = present ? __ffs(present) - 1 : 31;
-            present &= present - 1;
-            pr[u] = __shfl_sync(0xffffffffu, my_prow, e[u]);        // lane 31 holds -1
-        }
+            for (int u = 0; u < 4; ++u) {
+                e[u] = present ? __ffs(present) - 1 : 31;
+                present &= present - 1;
+                pr[u] = __shfl_sync(0xffffffffu, my_prow, e[u]);        // lane 31 holds -1
+            }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int ex = e[u] % 3 - 1, ey = (e[u] / 3) % 3 - 1, ez = e[u] / 9 - 1;
-            const int k = (bx - 2 * ex + 2) + 5 * (by - 2 * ey + 2) + 25 * (bz - 2 * ez + 2);
-            const bool ok = pr[u] >= 0 && ((reach >> e[u]) & 1u);
-            v[u] = ok ? __ldg(reinterpret_cast<const uint4 *>(T + (long)pr[u] * t_row + (long)k * cout) + part) : make_uint4(0, 0, 0, 0);
-            if (!ok) pr[u] = -1;
-        }
+            for (int u = 0; u < 4; ++u) {
+                const int ex = e[u] % 3 - 1, ey = (e[u] / 3) % 3 - 1, ez = e[u] / 9 - 1;
+                const int k = (bx - 2 * ex + 2) + 5 * (by - 2 * ey + 2) + 25 * (bz - 2 * ez + 2);
+                const bool ok = pr[u] >= 0 && ((reach >> e[u]) & 1u);
+                v[u] = ok ? __ldg(reinterpret_cast<const uint4 *>(T + (long)pr[u] * t_row + (long)k * cout) + part) : make_uint4(0, 0, 0, 0);
+                if (!ok) pr[u] = -1;
+            }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (pr[u] < 0) continue;                // absent / non-reaching parents add nothing
-            const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            for (int u = 0; u < 4; ++u) {
+                if (pr[u] < 0) continue;                // absent / non-reaching parents add nothing
+                const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                acc[2 * j] += __uint_as_float(w[j] << 16);
-                acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+                for (int j = 0; j < 4; ++j) {
+                    acc[2 * j] += __uint_as_float(w[j] << 16);
+                    acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+                }
             }
         }
-    }
-    if (!exists) return;
-    const long o = (long)__ldg(cell_base + cell) + __popc(cmask & ((1u << b) - 1u));
-    const int c0 = part * 8;
+        if (exists) {
+            const long o = (long)cbase + __popc(cmask & ((1u << b) - 1u));
+            const int c0 = part * 8;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = pcg_apply_act(acc[j] + (bias ? __ldg(bias + c0 + j) : 0.f), act);
-    if (out_f32) {
-        float4 *dst = reinterpret_cast<float4 *>(out_f32 + o * cout + c0);
-        dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    }
-    if (out_bf16) {
-        uint32_t pk[4];
+            for (int j = 0; j < 8; ++j) acc[j] = pcg_apply_act(acc[j] + (bias ? __ldg(bias + c0 + j) : 0.f), act);
+            if (out_f32) {
+                float4 *dst = reinterpret_cast<float4 *>(out_f32 + o * cout + c0);
+                dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+            }
+            if (out_bf16) {
+                uint32_t pk[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
-            pk[j] = *reinterpret_cast<uint32_t *>(&h);
+                for (int j = 0; j < 4; ++j) {
+                    __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+                    pk[j] = *reinterpret_cast<uint32_t *>(&h);
+                }
+                *reinterpret_cast<uint4 *>(out_bf16 + o * cout + c0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
         }
-        *reinterpret_cast<uint4 *>(out_bf16 + o * cout + c0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        cell = ncell; my_prow = nprow; cmask = ncmask; cbase = ncbase;
     }
 }
 
@@ -313,7 +332,10 @@ extern "C" int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnb
     const __nv_bfloat16 *T = reinterpret_cast<const __nv_bfloat16 *>(t_bf16);
     __nv_bfloat16 *ob = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
     const int lanes = cout / 8;
-    const unsigned blocks = (unsigned)cdiv(n_cells * 8 * lanes, 256);
+    long nb = cdiv(n_cells * 8 * lanes, 256);
+    static const long cap_blocks = getenv("PCG_REDUCE_BLOCKS") ? atol(getenv("PCG_REDUCE_BLOCKS")) : (long)PCG_SMS * 5 * 8;   // 8 units per warp at 5 blocks/SM
+    if (nb > cap_blocks) nb = cap_blocks;
+    const unsigned blocks = (unsigned)nb;
 #define PCG_REDUCE(L) k_cells_reduce<L><<<blocks, 256, 0, st>>>(T, cout, pnbr, pnbr_pitch, cell_mask, cell_base, n_cells, bias, act, out_f32, ob)
     switch (lanes) {
         case 4: PCG_REDUCE(4); break;
