@@ -330,7 +330,8 @@ def main():
         d = prof.get(kind, zero)
         gbs = d["bytes"] / (d["ms"] * 1e-3) / 1e9 if d["ms"] > 0 else 0.0
         return {"launches": d["launches"], "ms": round(d["ms"], 3), "algorithmic_gb": round(d["bytes"] / 1e9, 3), "achieved_gbs": round(gbs, 1),
-                "frac_of_hbm_peak": round(gbs / pk["hbm_gbs"], 4)}
+                "frac_of_hbm_peak": round(gbs / pk["hbm_gbs"], 4),
+                "ms_by_shape": {"x".join(map(str, k)): round(v[1], 3) for k, v in sorted(d["by_shape"].items(), key=lambda kv: -kv[1][1])}}
 
     traffic = None                      # DRAM bytes of the same launches from the committed ncu --set full capture
     tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
@@ -344,7 +345,7 @@ def main():
                 "per": "one frame (the roofline pass codes a single frame on one stream)",
                 "algorithmic_gflop_per_step": tc_flops / 1e9,
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},
-                "hbm_bound_kernels": {"gent_reduce (k_cells_reduce)": hbm("gent_reduce"), "conv_narrow (k_conv_mma)": hbm("conv_narrow"),
+                "hbm_bound_kernels": {"gent_reduce (k_cells_reduce)": hbm("gent_reduce"), "conv_narrow (occupancy-head layers, k_conv_tc_mt<1, 32|64|128>)": hbm("conv_narrow"),
                                       "gemm_first (k_gemm_first, T write)": hbm("gemm_first")},
                 "hbm_peak_gbs": pk["hbm_gbs"]}
     line = {"metric": METRIC, "value": total_points / (ms_res * 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -93,7 +93,8 @@ def test_two_tiles_per_cta_kernel_equals_single_tile_kernel(pkg, dev):
     down = cs.strided(2)
     up = down.generated(2, 2)
     cases = [(cs, cs, 3, False, 128, 64), (cs, cs, 3, False, 192, 256), (cs, cs, 3, False, 64, 32), (cs, down, 5, False, 128, 128),
-             (down, up, 2, True, 192, 192), (cs, cs, 1, False, 512, 128)]
+             (down, up, 2, True, 192, 192), (cs, cs, 1, False, 512, 128),
+             (cs, cs, 3, False, 32, 16), (cs, cs, 3, False, 16, 1), (cs, cs, 3, False, 64, 1), (cs, down, 5, False, 4, 32)]   # 64 / 32-byte rows
     prev_mode = so.set_conv_mode("tc")
     try:
         for in_set, out_set, ksize, transposed, cin, cout in cases:

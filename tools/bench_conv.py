@@ -66,3 +66,5 @@ with torch.no_grad():
     run("125x128x128 stride-8 set (14k)", cs8, cs8, 128, 128, 5)
     run("27x192x192 stride-8 set (14k)", cs8, cs8, 192, 192, 3)
     run("27x32x16   stride-1 set (818k)", cs1, cs1, 32, 16, 3)
+    run("27x16x1    stride-1 set (818k)", cs1, cs1, 16, 1, 3)
+    run("27x64x1    stride-1 set (818k)", cs1, cs1, 64, 1, 3)

@@ -84,20 +84,36 @@ __device__ __forceinline__ int tc_shfl_idx(int v, int src_lane) {      // volati
     asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(v), "r"(src_lane));
     return r;
 }
+template <int RB>
 __device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint8_t *fcol, int row_bytes, const int (&idx)[4], int lane) {
-    const int q = lane >> 3, c16 = lane & 7;
-    const uint32_t d0 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ q) << 4);
-    const uint32_t d1 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ (4 + q)) << 4);
+    // rows of RB bytes: LPR lanes per row, RPI rows per warp instruction.  fcol already points at this lane's 16-byte chunk of
+    // the operand columns.  Swizzle of the destination chunk: RB 128: c ^ (r & 7), 64: c ^ ((r >> 1) & 3), 32: c ^ ((r >> 2) & 1);
+    // with r = j*RPI + q the term depends on j only for RB = 128 (two per-lane constants), not at all for 64 / 32.
+    constexpr int LPR = RB / 16, RPI = 32 / LPR, NI = 128 / RPI;
+    const int q = lane / LPR, c16 = lane % LPR;
+    uint32_t d0, d1;
+    if (RB == 128) {
+        d0 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ q) << 4);
+        d1 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ (4 + q)) << 4);
+    } else {
+        const int x = RB == 64 ? ((q >> 1) & 3) : ((q >> 2) & 1);
+        d0 = d1 = dst_tile + (uint32_t)q * RB + (uint32_t)((c16 ^ x) << 4);
+    }
     asm volatile("" : "+l"(fcol));        // keep the column base one 64-bit addend of the multiply-add below
 #pragma unroll
-    for (int jb = 0; jb < 4; ++jb) {
+    for (int jb = 0; jb < NI / 8; ++jb) {
         int src[8];                       // eight shuffles in flight, then eight copies: the latencies overlap instead of adding up
 #pragma unroll
-        for (int u = 0; u < 8; ++u) src[u] = tc_shfl_idx(idx[jb], 4 * u + q);
+        for (int u = 0; u < 8; ++u) {
+            const int r0 = (8 * jb + u) * RPI;                      // first row of this instruction; row = r0 + q
+            src[u] = tc_shfl_idx(idx[r0 >> 5], (r0 & 31) + q);
+        }
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-            cp_async16(((u & 1) ? d1 : d0) + (uint32_t)((32 * jb + 4 * u) * 128), fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes,
+        for (int u = 0; u < 8; ++u) {
+            const int r0 = (8 * jb + u) * RPI;
+            cp_async16(((RB == 128 && (u & 1)) ? d1 : d0) + (uint32_t)(r0 * RB), fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes,
                        src[u] >= 0 ? 16u : 0u);
+        }
     }
 }
 
@@ -287,15 +303,16 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 // skips both its gather and its MMAs.  Per-element accumulation order is k_conv_tc's (ascending offset, chunk): same bits.
 // (A hybrid with tile 0 gathered by TMA gather4 and tile 1 by the LSU was measured and is slower than LSU-only: 0.68 vs 0.53 ms
 // on the 27x128x64 layer; the gather4 row rate, ~4 cycles per row per SM, paces the pair.)
-template <int T>
+template <int T, int RB>
 __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p) {
     constexpr int MMA_WARP = 4 * T;
+    constexpr uint32_t A_BYTES = TC_ROWS * RB;         // one gathered operand sub-tile (RB = 128 / 64 / 32-byte rows: cin_p >= 64 / 32 / 16)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     uint8_t *sm = smem_raw + (base - raw);
-    const uint32_t sub_b = (uint32_t)p.cout_p * 128u;
-    const uint32_t stage_bytes = T * TC_A_BYTES + sub_b;
+    const uint32_t sub_b = (uint32_t)p.cout_p * RB;
+    const uint32_t stage_bytes = T * A_BYTES + sub_b;
     uint8_t *ctl = sm + (size_t)p.stages * stage_bytes;
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(ctl);
     uint64_t *empty_bar = full_bar + TC_MAX_STAGES;
@@ -361,7 +378,7 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
         int a = 0, cc = g;
         while (cc >= p.chunks) { cc -= p.chunks; ++a; }
         const int32_t *nbr_t = p.nbr + (tile0 + t) * TC_ROWS + lane;
-        const uint8_t *fsrc = p.feats + (lane & 7) * 16;
+        const uint8_t *fsrc = p.feats + (lane % (RB / 16)) * 16;
         const int row_bytes = (int)p.row_bytes;
         int idx4[4];
         auto load_idx4 = [&](int a_) {
@@ -380,9 +397,9 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
             mbar_wait(smem_u32(empty_bar + s), (uint32_t)(wrap & 1) ^ 1u);
             if (t == 0 && lane == 0) {
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(sub_b) : "memory");
-                bulk_g2s(a_base + T * TC_A_BYTES, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
+                bulk_g2s(a_base + T * A_BYTES, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
             }
-            if (uses(t, k)) tc_lsu_gather_tile(a_base + (uint32_t)t * TC_A_BYTES, fsrc + cc * 128, row_bytes, idx4, lane);
+            if (uses(t, k)) tc_lsu_gather_tile<RB>(a_base + (uint32_t)t * A_BYTES, fsrc + cc * 128, row_bytes, idx4, lane);
             asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
             const int a_prev = a;
             s += P;
@@ -425,13 +442,13 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
                 fence_proxy_async();                 // cp.async wrote the operand rows through the generic proxy
                 tc_fence_after();
                 const uint32_t a_addr = base + (uint32_t)s * stage_bytes;
-                const uint64_t bdesc = umma_desc<128>(a_addr + T * TC_A_BYTES);
+                const uint64_t bdesc = umma_desc<RB>(a_addr + T * A_BYTES);
 #pragma unroll
                 for (int t = 0; t < T; ++t) {
                     if (!uses(t, k)) continue;
-                    const uint64_t adesc = umma_desc<128>(a_addr + t * TC_A_BYTES);
+                    const uint64_t adesc = umma_desc<RB>(a_addr + t * A_BYTES);
 #pragma unroll
-                    for (int kk = 0; kk < 4; ++kk)
+                    for (int kk = 0; kk < RB / 32; ++kk)
                         umma_bf16(tmem_d + (uint32_t)(t * p.cout_p), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc,
                                   (((started >> t) & 1u) | (uint32_t)kk) ? 1u : 0u);
                     started |= 1u << t;
@@ -570,23 +587,27 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.feats = reinterpret_cast<const uint8_t *>(feats_bf16);
     p.row_bytes = (long)cin_p * 2;
     cudaStream_t st = as_stream(stream);
-    if (rb == 128 && (p.cout_p & 31) == 0 && tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma"))) {
-        // 128-byte operand rows: LSU-gather kernel.  Static shape rule (measured with tools/bench_conv.py, profiles/r01_conv_variants.md):
+    if (tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma"))) {
+        // LSU-gather kernel.  Static shape rule (measured with tools/bench_conv.py, profiles/r01_conv_variants.md):
         //   at most one wave of tiles                        one tile per CTA, one CTA per SM, deepest ring
         //   wide outputs (weight slice >= 24 KiB per stage)  two tiles per CTA, one CTA per SM, deep ring
         //   large grids                                      two tiles per CTA, two CTAs per SM (16 producer warps per SM)
         //   other grids                                      one tile per CTA, three CTAs per SM (most independent pipelines)
+        //   narrow rows / outputs (heads in "tc" mode)       one tile per CTA, small stages, many CTAs per SM
         static const int mt_t = getenv("PCG_TC_MT_T") ? atoi(getenv("PCG_TC_MT_T")) : 0;          // tuning knobs: force T / the smem budget
         static const int mt_kb = getenv("PCG_TC_MT_SMEM_KB") ? atoi(getenv("PCG_TC_MT_SMEM_KB")) : 0;
+        static const int narrow_kb = getenv("PCG_TC_NARROW_KB") ? atoi(getenv("PCG_TC_NARROW_KB")) : 20;
         const long tiles = cdiv(n_out, TC_ROWS);
+        const bool wide = rb == 128 && (p.cout_p & 31) == 0;
         int T, kb;
-        if (tiles <= PCG_SMS) { T = 1; kb = 200; }                                  // at most one CTA per SM: deepest ring
+        if (!wide) { T = 1; kb = tiles <= PCG_SMS ? 100 : narrow_kb; }
+        else if (tiles <= PCG_SMS) { T = 1; kb = 200; }                             // at most one CTA per SM: deepest ring
         else if (p.cout_p > 128) { T = tiles >= 2 * PCG_SMS ? 2 : 1; kb = 200; }
         else if (tiles >= tc_mt_min_tiles()) { T = 2; kb = 104; }
         else { T = 1; kb = 70; }
-        if (mt_t == 1 || mt_t == 2) T = mt_t;
-        if (mt_kb > 0) kb = mt_kb;
-        const size_t stage_bytes = (size_t)T * TC_A_BYTES + (size_t)p.cout_p * 128;
+        if (wide && (mt_t == 1 || mt_t == 2)) T = mt_t;
+        if (wide && mt_kb > 0) kb = mt_kb;
+        const size_t stage_bytes = (size_t)T * TC_ROWS * rb + (size_t)p.cout_p * rb;
         int stages = (int)(((size_t)kb * 1024) / stage_bytes);
         if (stages < 2) stages = 2;
         if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
@@ -594,13 +615,16 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
         p.tmem_cols = 32;
         while (p.tmem_cols < T * p.cout_p) p.tmem_cols <<= 1;
         const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
-        if (T == 1) {
-            PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_conv_tc_mt<1><<<(unsigned)tiles, 160, smem, st>>>(p);
-        } else {
-            PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_conv_tc_mt<2><<<(unsigned)cdiv(tiles, 2), 288, smem, st>>>(p);
-        }
+#define PCG_MT(TT, RBB)                                                                                                   \
+    do {                                                                                                                  \
+        PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+        k_conv_tc_mt<TT, RBB><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p);                             \
+    } while (0)
+        if (rb == 32) PCG_MT(1, 32);
+        else if (rb == 64) PCG_MT(1, 64);
+        else if (T == 1) PCG_MT(1, 128);
+        else PCG_MT(2, 128);
+#undef PCG_MT
         PCG_LAUNCHED();
         return 0;
     }

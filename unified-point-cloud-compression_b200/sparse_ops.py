@@ -2,6 +2,7 @@
 feature lookup.  Host-side mirror of what MinkowskiEngine's CoordinateManager + pybind functions
 do for the reference; all arithmetic happens in the CUDA kernels.
 """
+import os
 import weakref
 
 import torch
@@ -429,8 +430,12 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
                                   "active_per_tile": act_mean, "transposed": bool(transposed), "e": (e0, e1)})
     # "tc" forces the tcgen05 kernel (tests pin its layouts on these shapes too); "auto" sends the narrow heads to the
     # register-gather mma.sync kernel
+    # (the LSU-gather tcgen05 kernel handles 32 / 64-byte rows too and is faster on the 32->16 and 64->1 heads -- level-3 candidates:
+    # 1.20 against 1.47 ms, level 2: 0.46 against 0.60 -- while the 16->1 layer stays on k_conv_mma, 0.68 against 0.76 ms;
+    # static shape rule, PCG_NARROW=mma sends every head layer to k_conv_mma for A/B runs)
     narrow = use_tc and _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
-        _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+        (cin <= 16 or os.environ.get("PCG_NARROW") == "mma") and _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+    is_head = cin <= 64 and cout <= 16          # gather-bound occupancy-head layers: reported with the HBM/L2-bound kernels
     if use_tc and _conv_mode == "auto" and feats.dtype == torch.float32 and im2col_eligible(K, cin, cout):
         rows = im2col_row_elems(K, cin)
         col = torch.empty((n_out, rows), dtype=torch.bfloat16, device=feats.device)
@@ -487,8 +492,12 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
              int(act), ptr(of), ptr(ob), stream())
         if prof is not None:
             e1.record()
-            prof.records.append(("conv_tc", (K, cin, cout), 2.0 * pairs * cin * cout,
-                                 2.0 * feats.shape[0] * cin + (4.0 if want_f32 else 2.0) * n_out * cout, e0, e1))
+            if is_head:
+                prof.records.append(("conv_narrow", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                     2.0 * feats.shape[0] * cin_padded(cin) + (4.0 if want_f32 else 2.0) * n_out * cout + 4.0 * K * n_out, e0, e1))
+            else:
+                prof.records.append(("conv_tc", (K, cin, cout), 2.0 * pairs * cin * cout,
+                                     2.0 * feats.shape[0] * cin + (4.0 if want_f32 else 2.0) * n_out * cout, e0, e1))
         if of is None:
             return ob
         if ob is not None:
