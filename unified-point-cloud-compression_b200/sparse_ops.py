@@ -618,8 +618,11 @@ def topk_mask(logits, coords, k_per_batch):
         return mask.view(torch.bool)
     lib = _lib.load()
     ws = scratch(lib.pcg_scratch_bytes(n), lg.device)
+    # one entry in k = one batch item in the tensor (transforms.py:228-254 loops over the batch items): no batch filter, so the
+    # radix passes read the logits only, not 16 bytes of coordinates per row
+    single = len(k_per_batch) == 1
     for b, k in enumerate(k_per_batch):
-        call("pcg_topk_mask", ptr(lg), ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
+        call("pcg_topk_mask", ptr(lg), None if single else ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
     return mask.view(torch.bool)          # the kernel writes 0 / 1
 
 
