@@ -14,6 +14,7 @@ N > 1     frames are independent: rank r codes frame seed r, no data-path collec
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload frame10|block128]
 """
 import argparse
+import gc
 import importlib
 import json
 import os
@@ -65,13 +66,19 @@ class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
-    def __init__(self, index):
+    def __init__(self, indexes):
+        """Rank 0 samples the clocks of every GPU of the job.  nvidia-smi's start-up takes driver-wide locks (seen as a
+        +20 ms first step on the other ranks when every rank started one after the barrier): wait for its first row here,
+        before the barrier that opens the timed region."""
         self.rows, self.proc = [], None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", ",".join(str(i) for i in indexes), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.perf_counter()
+            while not self.rows and time.perf_counter() - t0 < 3.0:
+                time.sleep(0.01)
         except Exception:
             self.proc = None
 
@@ -79,7 +86,12 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
+    def mark(self):
+        """Timed region starts here: rows sampled before are dropped."""
+        self.first = len(self.rows)
+
     def stop(self):
+        self.rows = self.rows[getattr(self, "first", 0):] or self.rows
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -267,12 +279,19 @@ def main():
             for _ in range(2):
                 pipe.map(step_resident, range(depth))
             barrier()
-        clocks = ClockSampler(local_rank)
+        # everything allocated so far (modules, torch, numpy) is long-lived: take it out of the collector's generations so that
+        # a full collection cannot stall a timed step for ~100 ms (seen as a one-off 130 ms e2e step at N=2)
+        gc.collect()
+        gc.freeze()
+        clocks = ClockSampler(range(local_rank, local_rank + world)) if rank == 0 else None
+        barrier()
+        if clocks is not None:
+            clocks.mark()
         l0 = pkg._lib.launch_count()
         t_res = timed(step_resident, args.steps)
         launches = (pkg._lib.launch_count() - l0) // max(args.steps, 1)
         barrier()
-        clk = clocks.stop()
+        clk = clocks.stop() if clocks is not None else None
         for _ in range(3):
             for j in range(depth):
                 step_e2e(j)

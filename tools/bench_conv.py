@@ -51,8 +51,21 @@ def run(name, in_set, out_set, cin, cout, ksize, reps=5):
 
 so.set_conv_mode("tc")
 print("PCG_TC_GATHER=%s PCG_TC_STAGES=%s PCG_TC_SMEM_KB=%s" % (os.environ.get("PCG_TC_GATHER"), os.environ.get("PCG_TC_STAGES"), os.environ.get("PCG_TC_SMEM_KB")))
+HEADS = "--heads" in sys.argv          # occupancy-head layers on the generative candidates (cell-major rows)
 QUICK = "--quick" in sys.argv          # two launches per shape, first two shapes only (for ncu captures)
 with torch.no_grad():
+    if HEADS:
+        so.set_conv_mode("auto")
+        print("PCG_TC_CA=%s PCG_TC_CARVEOUT=%s PCG_TC_NARROW_KB=%s PCG_NARROW=%s" % tuple(os.environ.get(k) for k in
+              ("PCG_TC_CA", "PCG_TC_CARVEOUT", "PCG_TC_NARROW_KB", "PCG_NARROW")))
+        cand1, cand2, cand4 = cs2.generated_cells(), cs4.generated_cells(), cs8.generated_cells()
+        run("27x32x16   level-3 candidates", cand1, cand1, 32, 16, 3)
+        run("27x16x1    level-3 candidates", cand1, cand1, 16, 1, 3)
+        run("27x128x64  level-2 candidates", cand2, cand2, 128, 64, 3)
+        run("27x64x1    level-2 candidates", cand2, cand2, 64, 1, 3)
+        run("27x128x64  level-1 candidates", cand4, cand4, 128, 64, 3)
+        run("27x64x1    level-1 candidates", cand4, cand4, 64, 1, 3)
+        sys.exit(0)
     if QUICK:
         run("27x128x64  stride-1 set (818k)", cs1, cs1, 128, 64, 3, reps=0)
         run("27x192x256 stride-2 set (214k)", cs2, cs2, 192, 256, 3, reps=0)

@@ -84,7 +84,7 @@ __device__ __forceinline__ int tc_shfl_idx(int v, int src_lane) {      // volati
     asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(v), "r"(src_lane));
     return r;
 }
-template <int RB>
+template <int RB, bool CA>
 __device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint8_t *fcol, int row_bytes, const int (&idx)[4], int lane) {
     // rows of RB bytes: LPR lanes per row, RPI rows per warp instruction.  fcol already points at this lane's 16-byte chunk of
     // the operand columns.  Swizzle of the destination chunk: RB 128: c ^ (r & 7), 64: c ^ ((r >> 1) & 3), 32: c ^ ((r >> 2) & 1);
@@ -111,8 +111,10 @@ __device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
             const int r0 = (8 * jb + u) * RPI;
-            cp_async16(((RB == 128 && (u & 1)) ? d1 : d0) + (uint32_t)(r0 * RB), fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes,
-                       src[u] >= 0 ? 16u : 0u);
+            const uint32_t dst = ((RB == 128 && (u & 1)) ? d1 : d0) + (uint32_t)(r0 * RB);
+            const uint8_t *from = fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes;
+            if (CA) cp_async16_ca(dst, from, src[u] >= 0 ? 16u : 0u);
+            else cp_async16(dst, from, src[u] >= 0 ? 16u : 0u);
         }
     }
 }
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 // skips both its gather and its MMAs.  Per-element accumulation order is k_conv_tc's (ascending offset, chunk): same bits.
 // (A hybrid with tile 0 gathered by TMA gather4 and tile 1 by the LSU was measured and is slower than LSU-only: 0.68 vs 0.53 ms
 // on the 27x128x64 layer; the gather4 row rate, ~4 cycles per row per SM, paces the pair.)
-template <int T, int RB>
+template <int T, int RB, bool CA>
 __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p) {
     constexpr int MMA_WARP = 4 * T;
     constexpr uint32_t A_BYTES = TC_ROWS * RB;         // one gathered operand sub-tile (RB = 128 / 64 / 32-byte rows: cin_p >= 64 / 32 / 16)
@@ -399,7 +401,7 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(sub_b) : "memory");
                 bulk_g2s(a_base + T * A_BYTES, p.wpacked + ((size_t)k * p.chunks + cc) * sub_b, sub_b, fb);
             }
-            if (uses(t, k)) tc_lsu_gather_tile<RB>(a_base + (uint32_t)t * A_BYTES, fsrc + cc * 128, row_bytes, idx4, lane);
+            if (uses(t, k)) tc_lsu_gather_tile<RB, CA>(a_base + (uint32_t)t * A_BYTES, fsrc + cc * 128, row_bytes, idx4, lane);
             asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
             const int a_prev = a;
             s += P;
@@ -615,15 +617,28 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
         p.tmem_cols = 32;
         while (p.tmem_cols < T * p.cout_p) p.tmem_cols <<= 1;
         const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
-#define PCG_MT(TT, RBB)                                                                                                   \
+        // tuning knobs: PCG_TC_CA bit 0 = narrow rows (RB 32 / 64), bit 1 = 128-byte rows gathered with cp.async.ca (L1-allocating);
+        // PCG_TC_CARVEOUT = preferred shared-memory share of the unified L1 in percent (what is left caches the gathered rows)
+        static const int ca_bits = getenv("PCG_TC_CA") ? atoi(getenv("PCG_TC_CA")) : 0;
+        static const int carveout = getenv("PCG_TC_CARVEOUT") ? atoi(getenv("PCG_TC_CARVEOUT")) : -1;
+        const bool ca = rb == 128 ? (ca_bits & 2) != 0 : (ca_bits & 1) != 0;
+#define PCG_MT(TT, RBB, CAA)                                                                                              \
     do {                                                                                                                  \
-        PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-        k_conv_tc_mt<TT, RBB><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p);                             \
+        PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, CAA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        if (carveout >= 0 && CAA)                                                                                         \
+            PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, CAA>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout)); \
+        k_conv_tc_mt<TT, RBB, CAA><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p);                        \
     } while (0)
-        if (rb == 32) PCG_MT(1, 32);
-        else if (rb == 64) PCG_MT(1, 64);
-        else if (T == 1) PCG_MT(1, 128);
-        else PCG_MT(2, 128);
+#define PCG_MT2(TT, RBB)                                                                                                  \
+    do {                                                                                                                  \
+        if (ca) PCG_MT(TT, RBB, true);                                                                                    \
+        else PCG_MT(TT, RBB, false);                                                                                      \
+    } while (0)
+        if (rb == 32) PCG_MT2(1, 32);
+        else if (rb == 64) PCG_MT2(1, 64);
+        else if (T == 1) PCG_MT2(1, 128);
+        else PCG_MT2(2, 128);
+#undef PCG_MT2
 #undef PCG_MT
         PCG_LAUNCHED();
         return 0;

@@ -434,7 +434,7 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     # 1.20 against 1.47 ms, level 2: 0.46 against 0.60 -- while the 16->1 layer stays on k_conv_mma, 0.68 against 0.76 ms;
     # static shape rule, PCG_NARROW=mma sends every head layer to k_conv_mma for A/B runs)
     narrow = use_tc and _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
-        (cin <= 16 or os.environ.get("PCG_NARROW") == "mma") and _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+        (cin <= 16 or os.environ.get("PCG_NARROW") == "mma") and os.environ.get("PCG_NARROW") != "tc" and _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
     is_head = cin <= 64 and cout <= 16          # gather-bound occupancy-head layers: reported with the HBM/L2-bound kernels
     if use_tc and _conv_mode == "auto" and feats.dtype == torch.float32 and im2col_eligible(K, cin, cout):
         rows = im2col_row_elems(K, cin)
