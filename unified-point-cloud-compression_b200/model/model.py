@@ -1,17 +1,22 @@
 """UnifiedModel -- mirror of /root/reference/model/model.py:15-250 (forward / compress / decompress).
 
-Same constructor config, sub-module names (g_a, g_s, entropy_model) and return conventions.  The
-bitstream container, the ASCII-PLY + tmc3 (G-PCC) side channel for the stride-8 coordinates
-(model.py:253-486) and Open3D are outside the graft: `compress(path=...)` / `decompress(path=...)`
-raise, the component form (`path=None`) is the supported interface -- exactly what the reference
-returns at model.py:186-187 and accepts at model.py:191.
+Same constructor config, sub-module names (g_a, g_s, entropy_model) and return conventions, both for the
+component form (`path=None`: what the reference returns at model.py:186-187 and accepts at model.py:191) and
+for the file form: `save_bitstream` / `load_bitstream` write the reference's container (model.py:253-385: same
+fields in the same order, big-endian as the `bitstream` package lays them out).  The one payload that differs is
+the stride-8 coordinate side channel: the reference shells out to the external G-PCC binary tmc3 through an ASCII
+PLY (model.py:388-486), which is not part of its tree; `gpcc_encode` / `gpcc_decode` here are a native lossless
+octree coder on the host (csrc/host_octree.cpp) with the same contract (a point SET in, bytes out, the set back).
 
 `encode_block` / `decode_block` expose the GPU halves with the host range coder factored out, which is
 what bench.py times (the coder stays on the host by design).
 """
+import struct
+
 import torch
 
 from .. import MinkowskiEngine as ME
+from .. import host_coder
 from .. import sparse_ops as so
 from ..compressai.models.base import CompressionModel
 from .entropy_models import MeanScaleHyperprior
@@ -88,8 +93,6 @@ class UnifiedModel(CompressionModel):
 
     # -- public API (model.py:94-250) ----------------------------------------------------------------
     def compress(self, pointcloud, q, path=None, block_size=1024, scaling_factor=1.0):
-        if path:
-            raise NotImplementedError("bitstream container + G-PCC side channel are outside the graft; use path=None")
         if scaling_factor != 1.0:
             pointcloud = pointcloud.clone()
             pointcloud[:, :3] = torch.round(pointcloud[:, :3] / scaling_factor).int()
@@ -102,11 +105,17 @@ class UnifiedModel(CompressionModel):
             _, strings, shape = self.entropy_model.compress(y, q)
             bitstreams.append(strings); shapes.append(shape); coords.append(y.C); q_vals.append(q); ks.append(k)
             start += count
+        if path:
+            self.save_bitstream(path, coords, bitstreams, shapes, ks, q_vals)
+            return None
         return bitstreams, shapes, ks, coords, q_vals
 
     def decompress(self, path=None, coordinates=None, strings=None, shape=None, k=None, q_vals=None):
         if path:
-            raise NotImplementedError("bitstream container + G-PCC side channel are outside the graft; pass the components")
+            coordinates, strings, shape, k, q_vals = self.load_bitstream(path)
+            dev = next(self.parameters()).device
+            coordinates = [torch.cat([torch.zeros((c.shape[0], 1), dtype=c.dtype), c], dim=1).to(dev) for c in coordinates]
+            q_vals = [qv.to(dev) for qv in q_vals]
         feats, pts = [], []
         for i, (b_strings, b_shape, b_coords, b_k) in enumerate(zip(strings, shape, coordinates, k)):
             b_coords = b_coords.to(torch.int32)
@@ -117,6 +126,75 @@ class UnifiedModel(CompressionModel):
             x_hat = self.g_s(y_hat, k=b_k)
             feats.append(x_hat.F); pts.append(x_hat.C)
         return self.finalize(torch.cat(pts, 0), torch.cat(feats, 0))
+
+    # -- bitstream container (model.py:253-385) ------------------------------------------------------
+    def save_bitstream(self, path, blocks_coordinates, blocks_strings, blocks_shapes, blocks_k, blocks_q):
+        """int32 n_blocks; per block: shape, len(points), q0, q1 (float64), len(y string), len(z string), k1, k2, k3,
+        then the three payloads -- the reference's field order (model.py:272-303)."""
+        out = [struct.pack(">i", len(blocks_coordinates))]
+        for points, strings, shape, k, q in zip(blocks_coordinates, blocks_strings, blocks_shapes, blocks_k, blocks_q):
+            assert len(strings) == 2 and all(len(s) == 1 for s in strings) and len(k) == 3 and all(len(v) == 1 for v in k), \
+                "one batch item per block (model.py:345-353 reads exactly two strings and three counts)"
+            points_bitstream = self.gpcc_encode(points, path)
+            out.append(b"".join(struct.pack(">i", int(v)) for v in shape))
+            out.append(struct.pack(">i", len(points_bitstream)))
+            out.append(struct.pack(">dd", float(q[0, 0]), float(q[0, 1])))
+            out.extend(struct.pack(">i", len(s[0])) for s in strings)
+            out.extend(struct.pack(">i", int(v[0])) for v in k)
+            out.append(points_bitstream)
+            out.extend(s[0] for s in strings)
+        with open(path, "wb") as f:
+            f.write(b"".join(out))
+
+    def load_bitstream(self, path):
+        """Inverse of `save_bitstream` (model.py:314-385); coordinates come back as (n,3) int32 CPU rows."""
+        with open(path, "rb") as f:
+            data = f.read()
+        pos = 0
+
+        def take(fmt):
+            nonlocal pos
+            vals = struct.unpack_from(fmt, data, pos)
+            pos += struct.calcsize(fmt)
+            return vals
+
+        def take_bytes(n):
+            nonlocal pos
+            if n < 0 or pos + n > len(data):
+                raise ValueError(f"{path}: truncated bitstream")
+            b = data[pos:pos + n]
+            pos += n
+            return b
+
+        try:
+            (num_blocks,) = take(">i")
+            coords, strings, shapes, ks, qs = [], [], [], [], []
+            for _ in range(num_blocks):
+                shape0, len_points = take(">II")
+                q0, q1 = take(">dd")
+                len_y, len_z, k1, k2, k3 = take(">IIIII")
+                points_bitstream = take_bytes(len_points)
+                strings.append([[take_bytes(len_y)], [take_bytes(len_z)]])
+                coords.append(self.gpcc_decode(points_bitstream, path))
+                shapes.append([int(shape0)])
+                ks.append([[int(k1)], [int(k2)], [int(k3)]])
+                qs.append(torch.tensor([q0, q1], dtype=torch.float64).reshape(1, 2).float())
+        except struct.error:
+            raise ValueError(f"{path}: truncated bitstream") from None
+        return coords, strings, shapes, ks, qs
+
+    def gpcc_encode(self, points, directory=None):
+        """Lossless bytes of the latent coordinates (rows [b,x,y,z], b = 0, stride-8 lattice).  Native octree coder in
+        place of the reference's tmc3 subprocess (model.py:388-431); `directory` is accepted and unused (no temp files)."""
+        pts = points.detach().to("cpu", torch.int32).numpy()
+        if pts.shape[0] and (pts[:, 0] != 0).any():
+            raise ValueError("gpcc_encode: a block holds one batch item (model.py:147-161)")
+        return host_coder.octree_encode(pts[:, 1:4], stride=8)
+
+    def gpcc_decode(self, bin, directory=None):
+        """Points of a `gpcc_encode` stream as (n,3) int32 xyz rows, like model.py:445-486 (the caller prepends the
+        batch column, model.py:216-220); Morton order -- the decoder re-derives its canonical row order anyway."""
+        return torch.from_numpy(host_coder.octree_decode(bytes(bin)))
 
     @staticmethod
     def finalize(coords, feats):
