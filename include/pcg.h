@@ -266,6 +266,20 @@ int pcg_nn_search(const uint64_t *keys, const int32_t *vals, long cap, const flo
                   const float *a_colors, long na, int max_radius, int32_t *nn_index, int32_t *nn_d2, float *yuv_sqerr,
                   int32_t *d_status, void *stream);
 
+/* ---- training-time augmentation of a cube (data/transform.py:33-124) -------------------------
+ * pcg_color_jitter: torchvision.transforms.ColorJitter semantics on n x 3 fp32 colour rows in [0,1] seen as a 3 x n x 1
+ * image (transform.py:50-53): the four ops (0 brightness, 1 contrast, 2 saturation, 3 hue) applied in the order op0..op3
+ * with the given factors; the contrast op blends with the mean grey level of the whole sample at that point of the chain.
+ * scratch: pcg_color_jitter_scratch_bytes() device bytes. */
+size_t pcg_color_jitter_scratch_bytes(void);
+int pcg_color_jitter(const float *colors, long n, int op0, int op1, int op2, int op3, float brightness, float contrast,
+                     float saturation, float hue, float *out, void *scratch, void *stream);
+/* pcg_rotate_floor: row i of (points - half) @ R^T + half, floored, as [0,x,y,z] int32 rows (transform.py:78-99 up to the
+ * de-duplication, which is pcg_unique_first).  rotation_host9: R row-major in HOST memory.  keep (optional): 1 where the
+ * rotated position lies in [0, crop_size)^3 (transform.py:86-89), all ones for crop_size <= 0. */
+int pcg_rotate_floor(const float *points, long n, const float *rotation_host9, float half, float crop_size,
+                     int32_t *out_coords, uint8_t *keep, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

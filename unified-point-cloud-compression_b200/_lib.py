@@ -59,6 +59,9 @@ _PROTOS = {
     "pcg_nn_search": (_I, [_P, _P, _L, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P]),
     "pcg_mask_to_rows": (_I, [_P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_gather_rows": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
+    "pcg_color_jitter_scratch_bytes": (_SZ, []),
+    "pcg_color_jitter": (_I, [_P, _L, _I, _I, _I, _I, _F, _F, _F, _F, _P, _P, _P]),
+    "pcg_rotate_floor": (_I, [_P, _L, _P, _F, _F, _P, _P, _P]),
     "pcg_features_at": (_I, [_P, _P, _L, _P, _I, _I, _P, _L, _P, _P]),
     "pcg_eb_likelihood": (_I, [_P, _L, _I, _L, _L, _P, _F, _P, _P]),
     "pcg_quantize": (_I, [_P, _P, _L, _I, _L, _L, _L, _L, _I, _P, _P, _P]),
