@@ -34,3 +34,26 @@ for name, par in (("stride-2 parents (214k)", cs1.strided(2)), ("stride-4 parent
     def whole():
         par._generated.clear(); par._kmaps.clear(); par.generated_cells()
     print(f"   generated_cells() end to end: {t(whole):.3f} ms")
+
+# GEMM-first transposed convolution on the same parents: per-kernel times from the conv profiler (PCG_REDUCE_VPL=1|2 for A/B)
+print("PCG_REDUCE_VPL=%s PCG_REDUCE_BLOCKS=%s" % (os.environ.get("PCG_REDUCE_VPL"), os.environ.get("PCG_REDUCE_BLOCKS")))
+for name, par, cin, cout in (("up_3: stride-2 parents, 128 -> 32", cs1.strided(2), 128, 32),
+                             ("up_2: stride-4 parents, 128 -> 128", cs1.strided(2).strided(2), 128, 128),
+                             ("up_1: stride-8 parents, 128 -> 128", cs1.strided(2).strided(2).strided(2), 128, 128)):
+    out_set = par.generated_cells()
+    f = so.to_bf16(torch.randn(par.n, cin, device=dev))
+    w = torch.randn(125, cin, cout, device=dev) * 0.05
+    pw = so.PackedGemmWeights()
+    so.profiler = so.ConvProfiler()
+    with torch.no_grad():
+        for i in range(7):
+            flush.fill_(1)
+            so.gen_conv_transpose_cells(f, par, out_set, w, None, packed=pw, out="both")
+    recs = so.profiler.records
+    torch.cuda.synchronize()
+    so.profiler = None
+    by = {}
+    for kind, shape, flops, bytes_, e0, e1 in recs[2 * (len(recs) // 7):]:
+        by.setdefault(kind, []).append((e0.elapsed_time(e1), bytes_))
+    msg = "  ".join(f"{k} {sorted(t for t, _ in v)[len(v) // 2]:.3f} ms ({v[0][1] / sorted(t for t, _ in v)[len(v) // 2] / 1e6:.0f} GB/s)" for k, v in by.items())
+    print(f"{name}: children={out_set.n}  {msg}")
