@@ -273,3 +273,20 @@ def test_generated_cells_empty_and_single(pkg, dev):
     assert torch.equal(nbr, plain.kernel_map(plain, 3, False)[0])
     empty = so.CoordSet(torch.zeros((0, 4), dtype=torch.int32, device=dev), 4).generated_cells()
     assert empty.n == 0 and empty.coords.shape == (0, 4)
+
+
+@pytest.mark.parametrize("n", [1, 2, 1023, 1024, 1025, 4096, 100_003, 9_000_001])
+@pytest.mark.parametrize("density", [0.0, 0.1, 0.93, 1.0])
+def test_compaction_keeps_input_order_at_every_tile_boundary(pkg, dev, n, density):
+    """Single-pass compaction (decoupled look-back over 1024-item tiles): the kept rows are exactly torch.nonzero's, in
+    input order, for sizes around the tile boundary and for a level-3-sized mask (thousands of tiles in flight)."""
+    so = pkg.sparse_ops
+    g = torch.Generator(device="cpu").manual_seed(n % 1000 + int(density * 100))
+    mask = (torch.rand(n, generator=g) < density).to(dev)
+    coords = torch.stack([torch.zeros(n, dtype=torch.int32), torch.arange(n, dtype=torch.int32) % 30000,
+                          torch.arange(n, dtype=torch.int32) // 30000, torch.zeros(n, dtype=torch.int32)], dim=1).to(dev)
+    feats = torch.arange(n, dtype=torch.float32, device=dev).reshape(n, 1)
+    oc, of = so.prune_rows(coords, feats, mask)
+    want = torch.nonzero(mask).reshape(-1)
+    assert oc.shape[0] == want.shape[0]
+    assert torch.equal(of.reshape(-1).long(), want) and torch.equal(oc, coords[want])

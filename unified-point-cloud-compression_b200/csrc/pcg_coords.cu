@@ -332,12 +332,13 @@ extern "C" int pcg_generate_coords(const int32_t *coords, long n, int ksize, int
 }
 
 // ---------------------------------------------------------------------------- kernel map
-// One CTA = one 128-row output tile x KM_SLICES offset slices: thread (r, s) owns row r and walks offsets s, s+S, ...
+// One CTA = one 128-row output tile x S = blockDim.y offset slices: thread (r, s) owns row r and walks offsets s, s+S, ...
 // (the coordinate is one int4 load; nbr[k][tile rows] is written as one coalesced 512 B line per offset).  Slicing the
 // offsets over threadIdx.y shortens the chain of dependent table probes per thread 4x and fills the machine on the
 // small strided sets (54 k / 13 k rows = 425 / 107 tiles), where one thread per row left most SMs idle.
-#define KM_SLICES 4
-__global__ void __launch_bounds__(128 * KM_SLICES) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
+// Small sets (at most two waves of tiles) take 8 slices: 1024 threads per CTA, 16 instead of 32 dependent probes for k = 5.
+#define KM_SLICES_MAX 8
+__global__ void __launch_bounds__(128 * KM_SLICES_MAX) k_kernel_map(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals,
                                                                 uint64_t mask, const int32_t *__restrict__ out_coords, long n_out,
                                                                 int ksize, int K, int step, int lattice, int32_t *__restrict__ nbr,
                                                                 long pitch, uint32_t *__restrict__ tile_mask) {
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(128 * KM_SLICES) k_kernel_map(const uint64_t *
     __syncthreads();
     const int lo = (ksize & 1) ? -(ksize >> 1) : 0;
     const int k2 = ksize * ksize;
-    for (int k = threadIdx.y; k < K; k += KM_SLICES) {
+    for (int k = threadIdx.y; k < K; k += blockDim.y) {
         const int iz = k / k2, iy = (k - iz * k2) / ksize, ix = k - iz * k2 - iy * ksize;
         int row = -1;
         if (live) {
@@ -382,7 +383,8 @@ extern "C" int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long ca
                   pcg_nbr_pitch(n_out));
     if (n_out <= 0) return 0;
     int step = transposed ? -ts : ts;
-    k_kernel_map<<<(unsigned)cdiv(n_out, 128), dim3(128, KM_SLICES), 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
+    const int slices = (cdiv(n_out, 128) <= 2 * PCG_SMS && K >= 64) ? KM_SLICES_MAX : 4;
+    k_kernel_map<<<(unsigned)cdiv(n_out, 128), dim3(128, slices), 0, as_stream(stream)>>>(keys, vals, (uint64_t)cap - 1, out_coords, n_out,
                                                                            ksize, K, step, in_lattice, nbr, nbr_pitch, tile_mask);
     PCG_LAUNCHED();
     return 0;
