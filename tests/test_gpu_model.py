@@ -254,3 +254,45 @@ def test_file_round_trip_equals_component_round_trip(pkg, dev, tmp_path, block_s
     size = os.path.getsize(path)
     assert payload < size < payload + len(coords) * (48 + 24 + 8) + sum(c.shape[0] for c in coords)   # header + side channel stay small
     print(f"block_size={block_size}: {len(coords)} blocks, {size} bytes, {8 * size / len(pts):.3f} bpp")
+
+
+def test_profiler_spans_cover_hash_map_and_entropy_calls(pkg, dev):
+    """bench.py's roofline pass: with sparse_ops.profiler set, one coded frame records CUDA-event spans (positive time, positive
+    algorithmic bytes) for the coordinate hash, the kernel maps, the compaction / top-k calls and the entropy-model kernels next
+    to the convolution kernels, and the coded result is unchanged by profiling."""
+    import importlib
+    from oracle import synth
+    from tests.helpers import model_config, spread_weights
+    model_mod = importlib.import_module(pkg.__name__ + ".model")
+    so = pkg.sparse_ops
+    torch.manual_seed(0)
+    net = model_mod.UnifiedModel(model_config(width=64))
+    spread_weights(net)
+    net = net.to(dev).eval()
+    net.update()
+    q = torch.tensor([[0.5, 0.5]], device=dev)
+    pts, rgb = synth.small_cloud(seed=3, radius=11.0, centre=(20, 20, 20), n_samples=9000)
+    cloud = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).to(dev)
+
+    def code():
+        enc = net.encode_block(cloud, q)
+        ys = enc["y_symbols"]
+        x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], q)
+        return enc["y_symbols"].clone(), net.finalize(x_hat.C, x_hat.F)
+
+    with torch.no_grad():
+        ref = code()
+        so.profiler = so.ConvProfiler()
+        try:
+            got = code()
+            summary = so.profiler.summary()
+        finally:
+            so.profiler = None
+    assert all(torch.equal(a, b) for a, b in zip(ref, got))
+    for kind in ("stride_coords", "kernel_map", "topk", "gather_rows", "entropy", "conv_tc"):
+        assert kind in summary, (kind, sorted(summary))
+    assert ("cells_kernel_map3" in summary) == ("gent_reduce" in summary)      # the octree-cell path brings its own 3x3x3 map
+    for kind, d in summary.items():
+        assert d["launches"] >= 1 and d["ms"] > 0 and d["bytes"] > 0, kind
+        if not kind.startswith("conv") and kind not in ("gemm_first", "gent_reduce"):
+            assert d["flops"] == 0, kind

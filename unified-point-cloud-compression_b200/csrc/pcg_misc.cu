@@ -344,6 +344,7 @@ struct TopkState {
     uint32_t prefix_mask;  // which bits of prefix are decided
     long long k_rem;       // how many still to take among keys matching prefix
     int hist[256];
+    unsigned done;         // CTAs of the current histogram pass that have added their counts
 };
 
 __device__ __forceinline__ uint32_t pcg_order_key(float f) {
@@ -352,14 +353,19 @@ __device__ __forceinline__ uint32_t pcg_order_key(float f) {
 }
 
 __global__ void k_topk_init(TopkState *s, long k) {
-    if (threadIdx.x == 0) { s->prefix = 0; s->prefix_mask = 0; s->k_rem = k; }
+    if (threadIdx.x == 0) { s->prefix = 0; s->prefix_mask = 0; s->k_rem = k; s->done = 0; }
     for (int i = threadIdx.x; i < 256; i += blockDim.x) s->hist[i] = 0;
 }
 
-__global__ void k_topk_hist(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int batch,
-                            int shift, TopkState *s) {
+// One radix pass: histogram of the digit at `shift` over the keys that match the digits chosen so far, then the LAST CTA to add
+// its counts (ticket in s->done) picks the digit holding the k_rem-th largest key and clears the state for the next pass.  The
+// counts are integers, so the result does not depend on which CTA comes last.  blockDim.x must be 256 (one thread per digit).
+__global__ void __launch_bounds__(256) k_topk_hist(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int batch,
+                                                   int shift, TopkState *s) {
     __shared__ int h[256];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) h[i] = 0;
+    __shared__ long long suf[257];
+    __shared__ bool last;
+    h[threadIdx.x] = 0;
     __syncthreads();
     const uint32_t prefix = s->prefix, pmask = s->prefix_mask;
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -370,32 +376,35 @@ __global__ void k_topk_hist(const float *__restrict__ logits, const int32_t *__r
         if ((key & pmask) == prefix) atomicAdd(&h[(key >> shift) & 255], 1);
     }
     __syncthreads();
-    for (int j = threadIdx.x; j < 256; j += blockDim.x)
-        if (h[j]) atomicAdd(&s->hist[j], h[j]);
-}
-
-__global__ void k_topk_select(TopkState *s, int shift) {
-    // single thread: walk digits from the top until the cumulative count reaches k_rem
-    if (threadIdx.x == 0) {
-        long long k = s->k_rem, total = 0;
-        for (int d = 0; d < 256; ++d) total += s->hist[d];
-        if (k > total) k = total;          // fewer rows than k: take them all
-        int d = 255;
-        long long above = 0;
-        if (k > 0) {
-            for (; d > 0; --d) {
-                if (above + s->hist[d] >= k) break;
-                above += s->hist[d];
-            }
-        } else {
-            d = 255; above = 0;
-        }
-        s->prefix |= ((uint32_t)d << shift);
-        s->prefix_mask |= (255u << shift);
-        s->k_rem = k - above;              // to take among keys with this digit (0 when k == 0)
-    }
+    if (h[threadIdx.x]) atomicAdd(&s->hist[threadIdx.x], h[threadIdx.x]);
+    __threadfence();
     __syncthreads();
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) s->hist[i] = 0;
+    if (threadIdx.x == 0) last = atomicAdd(&s->done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // digit d = threadIdx.x; read through L2 (the line holding prefix / hist[0..] may sit stale in this SM's L1) and clear
+    const int d = threadIdx.x;
+    const long long cnt = atomicExch(&s->hist[d], 0);
+    long long k = s->k_rem;                // read by every thread before the chosen one rewrites it (barriers below)
+    suf[d] = cnt;
+    if (d == 0) suf[256] = 0;
+    __syncthreads();
+    // suffix sums suf[d] = number of matching keys with digit >= d (Hillis-Steele over 256 entries)
+    for (int off = 1; off < 256; off <<= 1) {
+        long long add = d + off < 256 ? suf[d + off] : 0;
+        __syncthreads();
+        suf[d] += add;
+        __syncthreads();
+    }
+    if (k > suf[0]) k = suf[0];            // fewer rows than k: take them all
+    // the largest digit with at least k keys at or above it (k == 0 -> digit 255, nothing above)
+    if (suf[d] >= k && (d == 255 || suf[d + 1] < k)) {
+        s->prefix = prefix | ((uint32_t)d << shift);
+        s->prefix_mask = pmask | (255u << shift);
+        s->k_rem = k - suf[d + 1];         // to take among keys with this digit (0 when k == 0)
+        s->done = 0;
+    }
 }
 
 __global__ void k_topk_above(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int batch,
@@ -445,8 +454,6 @@ extern "C" int pcg_topk_mask(const float *logits, const int32_t *coords, long n,
     if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
     for (int shift = 24; shift >= 0; shift -= 8) {
         k_topk_hist<<<(unsigned)blocks, 256, 0, st>>>(logits, coords, n, batch, shift, s);
-        PCG_LAUNCHED();
-        k_topk_select<<<1, 256, 0, st>>>(s, shift);
         PCG_LAUNCHED();
     }
     k_topk_above<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(logits, coords, n, batch, s, mask);

@@ -9,6 +9,12 @@ import torch
 from ._lib import call, ptr, stream
 
 
+def _span(kind, n, c, elems):
+    """bench.py's roofline pass: CUDA events + algorithmic bytes (4-byte elements read once / written once)."""
+    from . import sparse_ops
+    return sparse_ops.hbm_span("entropy", (kind, c), 4.0 * n * c * elems)
+
+
 def _as_cn(t):
     """View a (1,C,N) / (C,N) / (C,1,N)-style tensor as (n, c, stride_n, stride_c) without copying."""
     if t.dim() == 3:
@@ -62,7 +68,8 @@ def eb_likelihood(x, params, bound):
     _need(x)
     n, c, sn, sc = _as_cn(x)
     out = _same_layout_out(x, torch.float32)
-    call("pcg_eb_likelihood", ptr(x), n, c, sn, sc, ptr(params), float(bound), ptr(out), stream())
+    with _span("eb_likelihood", n, c, 2):
+        call("pcg_eb_likelihood", ptr(x), n, c, sn, sc, ptr(params), float(bound), ptr(out), stream())
     return out
 
 
@@ -77,10 +84,12 @@ def quantize(x, means, mode):
         msn = msc = 0
     if mode == "dequantize":
         out = _same_layout_out(x, torch.float32)
-        call("pcg_quantize", ptr(x), ptr(means), n, c, sn, sc, msn, msc, 0, ptr(out), None, stream())
+        with _span("quantize", n, c, 3):
+            call("pcg_quantize", ptr(x), ptr(means), n, c, sn, sc, msn, msc, 0, ptr(out), None, stream())
     elif mode == "symbols":
         out = _same_layout_out(x, torch.int32)
-        call("pcg_quantize", ptr(x), ptr(means), n, c, sn, sc, msn, msc, 1, None, ptr(out), stream())
+        with _span("quantize", n, c, 3):
+            call("pcg_quantize", ptr(x), ptr(means), n, c, sn, sc, msn, msc, 1, None, ptr(out), stream())
     else:
         raise ValueError(f'Invalid quantization mode: "{mode}"')
     return out
@@ -95,7 +104,8 @@ def dequantize(sym, means):
     else:
         msn = msc = 0
     out = _same_layout_out(sym, torch.float32)
-    call("pcg_dequantize", ptr(sym), ptr(means), n, c, sn, sc, msn, msc, ptr(out), stream())
+    with _span("dequantize", n, c, 3):
+        call("pcg_dequantize", ptr(sym), ptr(means), n, c, sn, sc, msn, msc, ptr(out), stream())
     return out
 
 
@@ -115,8 +125,9 @@ def gc_likelihood(x, scales, means, scale_bound, lik_bound):
     scales = _match(scales, x)
     means = _match(means, x) if means is not None else None
     out = _same_layout_out(x, torch.float32)
-    call("pcg_gc_likelihood", ptr(x), ptr(scales), ptr(means), n, c, sn, sc, float(scale_bound), float(lik_bound),
-         ptr(out), stream())
+    with _span("gc_likelihood", n, c, 4):
+        call("pcg_gc_likelihood", ptr(x), ptr(scales), ptr(means), n, c, sn, sc, float(scale_bound), float(lik_bound),
+             ptr(out), stream())
     return out
 
 
@@ -124,8 +135,9 @@ def gc_build_indexes(scales, table, scale_bound):
     _need(scales)
     n, c, sn, sc = _as_cn(scales)
     out = _same_layout_out(scales, torch.int32)
-    call("pcg_gc_build_indexes", ptr(scales), n, c, sn, sc, ptr(table.contiguous()), table.numel(), float(scale_bound),
-         ptr(out), stream())
+    with _span("gc_build_indexes", n, c, 2):
+        call("pcg_gc_build_indexes", ptr(scales), n, c, sn, sc, ptr(table.contiguous()), table.numel(), float(scale_bound),
+             ptr(out), stream())
     return out
 
 
@@ -148,6 +160,7 @@ def gc_dequant_offsets(q, scales_hat, means_hat, gain, rescale, mlp, scale_bound
         gain = gain.contiguous()
     _, _, gsn, gsc = _as_cn(gain)
     out = _same_layout_out(q, torch.float32)
-    call("pcg_gc_dequant_offsets", ptr(q), ptr(scales_hat), ptr(means_hat), ptr(gain), ptr(rescale), n, c, sn, sc,
-         gsn, gsc, ptr(mlp), float(scale_bound), ptr(out), stream())
+    with _span("gc_dequant_offsets", n, c, 4):
+        call("pcg_gc_dequant_offsets", ptr(q), ptr(scales_hat), ptr(means_hat), ptr(gain), ptr(rescale), n, c, sn, sc,
+             gsn, gsc, ptr(mlp), float(scale_bound), ptr(out), stream())
     return out

@@ -2,6 +2,7 @@
 feature lookup.  Host-side mirror of what MinkowskiEngine's CoordinateManager + pybind functions
 do for the reference; all arithmetic happens in the CUDA kernels.
 """
+import contextlib
 import os
 import weakref
 
@@ -72,7 +73,8 @@ class CoordSet:
             cap = _lib.load().pcg_hash_capacity(max(self.n, 1))
             keys = torch.empty(cap, dtype=torch.int64, device=dev)
             vals = torch.empty(cap, dtype=torch.int32, device=dev)
-            call("pcg_hash_build", ptr(self.coords), self.n, ptr(keys), ptr(vals), cap, stream())
+            with hbm_span("hash_build", (self.n,), 16.0 * self.n + 12.0 * cap):      # coordinates read, table (key + row) written
+                call("pcg_hash_build", ptr(self.coords), self.n, ptr(keys), ptr(vals), cap, stream())
             self._table = (keys, vals, cap)
         return self._table
 
@@ -101,8 +103,9 @@ class CoordSet:
             cnt = torch.zeros(1, dtype=torch.int32, device=dev)
             nb = _lib.load().pcg_scratch_bytes(max(self.n, 1))
             ws = scratch(nb, dev)
-            call("pcg_stride_coords", ptr(self.coords), self.n, step, ptr(keys), ptr(vals), cap, ptr(out), ptr(cnt),
-                 ptr(ws), ws.numel(), stream())
+            with hbm_span("stride_coords", (self.n,), 16.0 * self.n + 12.0 * cap):      # lower bound: the 16 * n_out written rows not counted
+                call("pcg_stride_coords", ptr(self.coords), self.n, step, ptr(keys), ptr(vals), cap, ptr(out), ptr(cnt),
+                     ptr(ws), ws.numel(), stream())
             n_out = int(cnt.item())
             hit = CoordSet(out[:n_out], step, table=(keys, vals, cap))
             self._strided[stride] = hit
@@ -128,8 +131,9 @@ class CoordSet:
                 out = torch.empty((max(max_out, 1), 4), dtype=torch.int32, device=dev)
                 cnt = torch.zeros(2, dtype=torch.int32, device=dev)
                 ws = scratch(lib.pcg_scratch_bytes(max(n_cand, 1)), dev)
-                call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), int(stride), ts_out, ptr(keys), ptr(vals), cap,
-                     ptr(out), max_out, ptr(cnt[0:1]), ptr(cnt[1:2]), ptr(ws), ws.numel(), stream())
+                with hbm_span("generate_coords", (self.n, K), 16.0 * self.n + 12.0 * cap):   # lower bound, as above
+                    call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), int(stride), ts_out, ptr(keys), ptr(vals), cap,
+                         ptr(out), max_out, ptr(cnt[0:1]), ptr(cnt[1:2]), ptr(ws), ws.numel(), stream())
                 n_out, status = (int(v) for v in cnt.tolist())
                 if status & 2:
                     raise RuntimeError("generated coordinate outside the 16-bit packing range")
@@ -201,8 +205,10 @@ class CoordSet:
             nbr = torch.empty((K, pitch), dtype=torch.int32, device=dev)
             tiles = (out_set.n + 127) // 128
             tmask = torch.empty((max(tiles, 1), 4), dtype=torch.int32, device=dev) if K <= 128 else None
-            call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
-                 int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), pitch, ptr(tmask), stream())
+            # output coordinates read once, the table read once (lower bound of K probes per row), neighbour table written
+            with hbm_span("kernel_map", (K, out_set.n), 16.0 * out_set.n + 12.0 * cap + 4.0 * K * pitch):
+                call("pcg_kernel_map", ptr(keys), ptr(vals), cap, ptr(out_set.coords), out_set.n, int(ksize), ts,
+                     int(bool(transposed)), self.ts if transposed else 0, ptr(nbr), pitch, ptr(tmask), stream())
             hit = (nbr, tmask, None if out_set is self else out_set)   # keep out_set alive while cached (id() key)
             self._kmaps[key] = hit
         return hit[0], hit[1]
@@ -231,8 +237,9 @@ class CellCoordSet(CoordSet):
             pitch = _lib.load().pcg_nbr_pitch(self.n)
             nbr = torch.empty((27, pitch), dtype=torch.int32, device=dev)
             tmask = torch.empty((max((self.n + 127) // 128, 1), 4), dtype=torch.int32, device=dev)
-            call("pcg_cells_kernel_map3", ptr(ckeys), ptr(cvals), ccap, ptr(self.coords), ptr(self.out_cell), self.n, self.ts,
-                 ptr(self.cell_mask), ptr(self.cell_base), ptr(nbr), pitch, ptr(tmask), stream())
+            with hbm_span("cells_kernel_map3", (27, self.n), 20.0 * self.n + 12.0 * ccap + 5.0 * self.cells.n + 4.0 * 27 * pitch):
+                call("pcg_cells_kernel_map3", ptr(ckeys), ptr(cvals), ccap, ptr(self.coords), ptr(self.out_cell), self.n, self.ts,
+                     ptr(self.cell_mask), ptr(self.cell_base), ptr(nbr), pitch, ptr(tmask), stream())
             hit = (nbr, tmask, None)
             self._kmaps[key] = hit
         return hit[0], hit[1]
@@ -378,6 +385,21 @@ class ConvProfiler:
 
 
 profiler = None      # set to a ConvProfiler() to time every convolution launch
+
+
+@contextlib.contextmanager
+def hbm_span(kind, shape, nbytes):
+    """CUDA events around one HBM-bound C-ABI call (hash, kernel map, compaction, entropy model) when a profiler is set.
+    nbytes = ALGORITHMIC bytes of the call: inputs read once + outputs written once."""
+    prof = profiler
+    if prof is None:
+        yield
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    yield
+    e1.record()
+    prof.records.append((kind, shape, 0.0, float(nbytes), e0, e1))
 
 
 def im2col_row_elems(K, cin):
@@ -622,7 +644,8 @@ def topk_mask(logits, coords, k_per_batch):
     # radix passes read the logits only, not 16 bytes of coordinates per row
     single = len(k_per_batch) == 1
     for b, k in enumerate(k_per_batch):
-        call("pcg_topk_mask", ptr(lg), None if single else ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
+        with hbm_span("topk", (n,), 4.0 * n + 1.0 * n):          # logits read once, mask written (the radix passes re-read: not algorithmic)
+            call("pcg_topk_mask", ptr(lg), None if single else ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
     return mask.view(torch.bool)          # the kernel writes 0 / 1
 
 
@@ -649,8 +672,10 @@ def gather_rows(coords, feats, rows):
     dev = rows.device
     oc = torch.empty((n, 4), dtype=torch.int32, device=dev) if coords is not None else None
     of = torch.empty((n, feats.shape[1]), dtype=torch.float32, device=dev) if feats is not None else None
-    call("pcg_gather_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, feats.shape[1] if feats is not None else 0,
-         ptr(rows), n, ptr(oc), ptr(of), stream())
+    row_bytes = (16 if coords is not None else 0) + (4 * feats.shape[1] if feats is not None else 0)
+    with hbm_span("gather_rows", (n, row_bytes), (4.0 + 2.0 * row_bytes) * n):        # row list + rows read + rows written
+        call("pcg_gather_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, feats.shape[1] if feats is not None else 0,
+             ptr(rows), n, ptr(oc), ptr(of), stream())
     return oc, of
 
 
@@ -680,5 +705,6 @@ def features_at(feats, cset, query):
     q = query.to(device=feats.device, dtype=torch.float32).contiguous()
     f = feats.contiguous()
     out = torch.empty((q.shape[0], f.shape[1]), dtype=torch.float32, device=f.device)
-    call("pcg_features_at", ptr(keys), ptr(vals), cap, ptr(f), f.shape[1], cset.ts, ptr(q), q.shape[0], ptr(out), stream())
+    with hbm_span("features_at", (q.shape[0], f.shape[1]), 16.0 * q.shape[0] + 8.0 * q.shape[0] * f.shape[1]):
+        call("pcg_features_at", ptr(keys), ptr(vals), cap, ptr(f), f.shape[1], cset.ts, ptr(q), q.shape[0], ptr(out), stream())
     return out
