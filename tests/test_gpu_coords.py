@@ -163,7 +163,7 @@ def test_prune_rows_reordered_equals_prune_then_morton_sort(pkg, dev, n, c):
     assert torch.equal(gc, oc) and torch.equal(gf, of)
 
 
-@pytest.mark.parametrize("n,k", [(10, 3), (5000, 1234), (5000, 0), (5000, 5000), (5000, 7000), (70000, 35000)])
+@pytest.mark.parametrize("n,k", [(10, 3), (5000, 1234), (5000, 0), (5000, 5000), (5000, 7000), (70000, 35000), (3000000, 1000001)])
 def test_topk_mask(pkg, dev, n, k):
     so = pkg.sparse_ops
     rng = np.random.default_rng(k + n)
