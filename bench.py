@@ -337,7 +337,7 @@ def main():
     zero = {"ms": 0.0, "flops": 0.0, "bytes": 0.0, "launches": 0, "by_shape": {}}
     tcs = [prof.get(k, zero) for k in ("conv_tc", "gemm_first")]
     tc_ms, tc_flops, tc_launches = (sum(t[k] for t in tcs) for k in ("ms", "flops", "launches"))
-    all_conv_ms = sum(v["ms"] for k, v in prof.items() if k in ("conv_tc", "gemm_first", "gent_reduce", "conv_narrow", "conv_f32"))
+    all_conv_ms = sum(v["ms"] for k, v in prof.items() if k in ("conv_tc", "gemm_first", "gent_reduce", "conv_narrow", "conv_f32", "head_gather"))
     achieved = tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
 
     def shapes(kind):
@@ -366,6 +366,7 @@ def main():
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},
                 "hbm_bound_kernels": {"gent_reduce (k_cells_reduce)": hbm("gent_reduce"), "conv_narrow (occupancy-head layers, k_conv_tc_mt<1, 32|64|128>)": hbm("conv_narrow"),
                                       "gemm_first (k_gemm_first, T write)": hbm("gemm_first"),
+                                      "head_gather (k_gather_sum: second head layer, GEMM-first)": hbm("head_gather"),
                                       # north-star pieces 1 and 5: coordinate hash, kernel maps, compaction, entropy model (CUDA events per C-ABI call)
                                       "hash_build (k_hash_insert)": hbm("hash_build"),
                                       "stride_coords (k_insert_strided + compaction)": hbm("stride_coords"),

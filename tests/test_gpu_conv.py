@@ -212,6 +212,50 @@ def test_topk_selection_consistent_with_fp32_logits(pkg, dev):
     print(f"top-k agreement with the fp32 selection: {(mask & exact).sum() / k:.4f} (error band {band:.2e}, logit std {ref.std():.2e})")
 
 
+@pytest.mark.parametrize("cin,cmid", [(32, 16), (128, 64), (64, 32)])
+def test_fused_occupancy_head_matches_oracle_and_two_layer_path(pkg, dev, cin, cmid):
+    """sparse_ops.occupancy_head (second head layer GEMM-first out of the first layer's tcgen05 epilogue + pcg_gather_sum) against the
+    fp32 oracle (1e-2 relative L2, north-star) and against the two-convolution path it replaces (which rounds the hidden row to bf16:
+    the fused form must be at least as close to the oracle); integer-valued operands must come out exactly; run-to-run identical."""
+    so = pkg.sparse_ops
+    C, cs = setup(dev, pkg, seed=23, ts=2)
+    cand = cs.generated(5, 2)
+    Cc = cand.coords.cpu().numpy()
+    n = len(Cc)
+    rng = np.random.default_rng(cin + cmid)
+    X = rng.standard_normal((n, cin)).astype(np.float32)
+    W1 = (rng.standard_normal((27, cin, cmid)) / np.sqrt(cin * 27) * 2).astype(np.float32)
+    b1 = (rng.standard_normal((1, cmid)) * 0.1).astype(np.float32)
+    W2 = (rng.standard_normal((27, cmid, 1)) / np.sqrt(cmid * 27) * 2).astype(np.float32)
+    b2 = np.full((1, 1), 0.25, np.float32)
+    nbr = native.kernel_map(Cc, Cc, 3, 1, False)
+    ref = native.conv(native.conv(X, nbr, W1, b1, 1), nbr, W2, b2, 0)[:, 0]
+    t = lambda a: torch.from_numpy(a).to(dev)
+    assert so.head_fusable(3, t(W1), 3, t(W2))
+    fused = so.occupancy_head(t(X), cand, t(W1), t(b1), t(W2), t(b2))
+    assert fused.shape == (n, 1)
+    again = so.occupancy_head(t(X), cand, t(W1), t(b1), t(W2), t(b2))
+    assert torch.equal(fused, again)
+    prev = so.set_conv_mode("tc")
+    try:
+        h = so.sparse_conv(t(X), cand, cand, t(W1), t(b1), 3, False, act=so.ACT_RELU, out="bf16")
+        two = so.sparse_conv(h, cand, cand, t(W2), t(b2), 3, False)[:, 0].cpu().numpy()
+    finally:
+        so.set_conv_mode(prev)
+    mine = fused[:, 0].cpu().numpy()
+    e_fused, e_two = rel_l2(mine, ref), rel_l2(two, ref)
+    print(f"fused head {cin}->{cmid}->1: rel L2 {e_fused:.2e} (two-layer bf16 path {e_two:.2e})")
+    assert e_fused < 1e-2 and e_fused <= e_two * 1.05 + 1e-6
+    # small integers: every product and partial sum is exact in bf16 x bf16 -> fp32, so the result must equal the oracle bit for bit
+    Xi = rng.integers(-2, 3, (n, cin)).astype(np.float32)
+    W1i = rng.integers(-1, 2, (27, cin, cmid)).astype(np.float32)
+    W2i = rng.integers(-1, 2, (27, cmid, 1)).astype(np.float32)
+    b1i = rng.integers(-3, 4, (1, cmid)).astype(np.float32)
+    refi = native.conv(native.conv(Xi, nbr, W1i, b1i, 1), nbr, W2i, b2 * 4, 0)[:, 0]
+    gi = so.occupancy_head(t(Xi), cand, t(W1i), t(b1i), t(W2i), t(b2 * 4))[:, 0].cpu().numpy()
+    assert np.array_equal(gi, refi)
+
+
 @pytest.mark.parametrize("cin,cout,kind", [(128, 128, "surface"), (128, 32, "surface"), (64, 32, "scattered"), (64, 64, "surface")])
 def test_gen_conv_transpose_cells_matches_oracle(pkg, dev, cin, cout, kind):
     """Kernel-5/stride-2 generative transposed convolution on the octree-cell path (GEMM-first + gather-reduce) vs the

@@ -38,6 +38,8 @@ _PROTOS = {
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),
     "pcg_pack_weights_bf16": (_I, [_P, _I, _I, _I, _P, _P]),
     "pcg_conv_fwd_tc": (_I, [_P, _L, _I, _P, _L, _P, _I, _L, _P, _P, _I, _I, _P, _P, _P]),
+    "pcg_conv_fwd_tc_proj": (_I, [_P, _L, _I, _P, _L, _P, _I, _L, _P, _P, _I, _I, _P, _P, _P, _I, _P, _L, _P]),
+    "pcg_gather_sum": (_I, [_P, _L, _P, _L, _I, _L, _P, _I, _P, _P]),
     "pcg_im2col_bf16": (_I, [_P, _I, _P, _L, _I, _L, _I, _P, _P]),
     "pcg_mma_weight_bytes": (_SZ, [_I, _I, _I]),
     "pcg_pack_weights_mma": (_I, [_P, _I, _I, _I, _P, _P]),

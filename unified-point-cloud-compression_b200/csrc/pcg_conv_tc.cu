@@ -42,6 +42,22 @@ struct TcParams {
     int stages;
     int tmem_cols;   // power of two >= max(32, cout_p)
     int act;
+    // fused second head layer (pcg_conv_fwd_tc_proj): proj_out[k][o] = act(row o) . w2[k][:] for the TC_PROJ_K offsets of the
+    // following cout -> 1 convolution, taken from the fp32 accumulator row in the epilogue (weights: kernel parameter TcProjW)
+    float *proj_out;              // [TC_PROJ_K][proj_pitch] fp32
+    long proj_pitch;
+};
+#define TC_PROJ_K 27
+// Second-layer weights [TC_PROJ_K][PC] of the fused head, passed BY VALUE as a kernel parameter: they sit in the constant bank, so
+// every FFMA of the epilogue projection takes its weight as a constant operand (no load instruction, no latency).
+// 27 x 64 x 4 B = 6.9 KB (kernel parameters may be up to 32 KB since CUDA 12.1).  PC = 0: no projection (empty).
+template <int PC>
+struct TcProjW {
+    float w[TC_PROJ_K * PC];
+};
+template <>
+struct TcProjW<0> {
+    char unused;
 };
 
 // epilogue piece shared by the tcgen05 conv kernels: 16 accumulator columns [c0, c0+16) of output row o -> bias, activation, fp32 and/or bf16
@@ -72,6 +88,13 @@ __device__ __forceinline__ void tc_store16(const TcParams &p, long o, int c0, co
         for (int j = 0; j < 16; ++j)
             if (c0 + j < p.cout) p.out_f32[o * p.cout + c0 + j] = f[j];
     }
+}
+
+// the same 16 columns after bias + activation, kept in registers (fused second head layer)
+__device__ __forceinline__ void tc_act16(const TcParams &p, int c0, const uint32_t (&v)[16], float (&f)[16]) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+        f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
 }
 
 // LSU gather of one 128-row x 128-byte operand sub-tile into its 128B-swizzled image at dst_tile.  Lane m holds the neighbour
@@ -305,8 +328,9 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 // skips both its gather and its MMAs.  Per-element accumulation order is k_conv_tc's (ascending offset, chunk): same bits.
 // (A hybrid with tile 0 gathered by TMA gather4 and tile 1 by the LSU was measured and is slower than LSU-only: 0.68 vs 0.53 ms
 // on the 27x128x64 layer; the gather4 row rate, ~4 cycles per row per SM, paces the pair.)
-template <int T, int RB, bool CA>
-__global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p) {
+// PC: 0 = plain; 16 / 32 / 64 = cout of a first head layer whose second layer (cout -> 1, 27 offsets) is folded into the epilogue.
+template <int T, int RB, bool CA, int PC = 0>
+__global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p, const TcProjW<PC> pw) {
     constexpr int MMA_WARP = 4 * T;
     constexpr uint32_t A_BYTES = TC_ROWS * RB;         // one gathered operand sub-tile (RB = 128 / 64 / 32-byte rows: cin_p >= 64 / 32 / 16)
     extern __shared__ uint8_t smem_raw[];
@@ -421,14 +445,43 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
         const bool has = (tmask_s[t * 4] | tmask_s[t * 4 + 1] | tmask_s[t * 4 + 2] | tmask_s[t * 4 + 3]) != 0u;
         const uint32_t lane_base = tmem_d + ((uint32_t)(g * 32) << 16) + (uint32_t)(t * p.cout_p);
         if (tile0 + t < n_tiles) {
-            for (int c0 = 0; c0 < p.cout; c0 += 16) {
-                uint32_t v[16];
-                if (has) tmem_ld16(lane_base + (uint32_t)c0, v);
-                else {
+            if constexpr (PC == 0) {
+                for (int c0 = 0; c0 < p.cout; c0 += 16) {
+                    uint32_t v[16];
+                    if (has) tmem_ld16(lane_base + (uint32_t)c0, v);
+                    else {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = 0u;
+                        for (int j = 0; j < 16; ++j) v[j] = 0u;
+                    }
+                    if (live) tc_store16(p, o, c0, v);
                 }
-                if (live) tc_store16(p, o, c0, v);
+            } else {
+                // fused second layer: ps[k] = act(row) . w2[k][:], columns ascending (one fixed fp32 chain per offset)
+                float ps[TC_PROJ_K];
+#pragma unroll
+                for (int k = 0; k < TC_PROJ_K; ++k) ps[k] = 0.f;
+#pragma unroll
+                for (int c0 = 0; c0 < PC; c0 += 16) {
+                    uint32_t v[16];
+                    if (has) tmem_ld16(lane_base + (uint32_t)c0, v);
+                    else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = 0u;
+                    }
+                    if (live) tc_store16(p, o, c0, v);
+                    float f[16];
+                    tc_act16(p, c0, v, f);
+#pragma unroll
+                    for (int k = 0; k < TC_PROJ_K; ++k) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) ps[k] = fmaf(f[j], pw.w[k * PC + c0 + j], ps[k]);
+                        if (PC == 16 && live) p.proj_out[(long)k * p.proj_pitch + o] = ps[k];   // single column group: store as formed
+                    }
+                }
+                if (PC != 16 && live) {
+#pragma unroll
+                    for (int k = 0; k < TC_PROJ_K; ++k) p.proj_out[(long)k * p.proj_pitch + o] = ps[k];   // lane = row: coalesced
+                }
             }
         }
         tc_fence_before();
@@ -552,9 +605,10 @@ static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cuda
     return 0;
 }
 
-extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
-                               int act, float *out_f32, void *out_bf16, void *stream) {
+static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                            const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                            int act, float *out_f32, void *out_bf16, const float *proj_w_host, float *proj_out, long proj_pitch,
+                            void *stream) {
     PCG_CHECK_ARG(cin >= 1 && cin <= 1024, "pcg_conv_fwd_tc: cin=%d", cin);
     PCG_CHECK_ARG(cout >= 1 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be in [1,256]", cout);
     PCG_CHECK_ARG(out_bf16 == nullptr || (cout & 15) == 0, "pcg_conv_fwd_tc: a bf16 output needs cout %% 16 == 0 (cout=%d)", cout);
@@ -588,8 +642,11 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     p.act = act;
     p.feats = reinterpret_cast<const uint8_t *>(feats_bf16);
     p.row_bytes = (long)cin_p * 2;
+    p.proj_out = proj_out; p.proj_pitch = proj_pitch;
+    const bool proj = proj_out != nullptr;
     cudaStream_t st = as_stream(stream);
-    if (tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma"))) {
+    // (the fused second head layer lives in the LSU-gather kernel only)
+    if (proj || (tc_mt_min_tiles() != 0 && !(getenv("PCG_TC_GATHER") && !strcmp(getenv("PCG_TC_GATHER"), "tma")))) {
         // LSU-gather kernel.  Static shape rule (measured with tools/bench_conv.py, profiles/r01_conv_variants.md):
         //   at most one wave of tiles                        one tile per CTA, one CTA per SM, deepest ring
         //   wide outputs (weight slice >= 24 KiB per stage)  two tiles per CTA, one CTA per SM, deep ring
@@ -627,17 +684,36 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
         PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, CAA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         if (carveout >= 0 && CAA)                                                                                         \
             PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, CAA>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout)); \
-        k_conv_tc_mt<TT, RBB, CAA><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p);                        \
+        k_conv_tc_mt<TT, RBB, CAA><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p, TcProjW<0>{});          \
     } while (0)
 #define PCG_MT2(TT, RBB)                                                                                                  \
     do {                                                                                                                  \
         if (ca) PCG_MT(TT, RBB, true);                                                                                    \
         else PCG_MT(TT, RBB, false);                                                                                      \
     } while (0)
-        if (rb == 32) PCG_MT2(1, 32);
+#define PCG_MTP(TT, RBB, PCC)                                                                                             \
+    do {                                                                                                                  \
+        TcProjW<PCC> pw;                                                                                                  \
+        memcpy(pw.w, proj_w_host, sizeof(pw.w));                                                                          \
+        PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, false, PCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        k_conv_tc_mt<TT, RBB, false, PCC><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p, pw);             \
+    } while (0)
+#define PCG_MTP3(PCC)                                                                                                     \
+    do {                                                                                                                  \
+        if (rb == 64) PCG_MTP(1, 64, PCC);                                                                                \
+        else if (T == 1) PCG_MTP(1, 128, PCC);                                                                            \
+        else PCG_MTP(2, 128, PCC);                                                                                        \
+    } while (0)
+        if (proj) {
+            if (cout == 16) PCG_MTP3(16);
+            else if (cout == 32) PCG_MTP3(32);
+            else PCG_MTP3(64);
+        } else if (rb == 32) PCG_MT2(1, 32);
         else if (rb == 64) PCG_MT2(1, 64);
         else if (T == 1) PCG_MT2(1, 128);
         else PCG_MT2(2, 128);
+#undef PCG_MTP3
+#undef PCG_MTP
 #undef PCG_MT2
 #undef PCG_MT
         PCG_LAUNCHED();
@@ -657,4 +733,59 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
     if (rb == 32) return launch_tc<32>(tm, p, smem, st);
     if (rb == 64) return launch_tc<64>(tm, p, smem, st);
     return launch_tc<128>(tm, p, smem, st);
+}
+
+extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                               const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                               int act, float *out_f32, void *out_bf16, void *stream) {
+    return conv_fwd_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
+                            nullptr, nullptr, 0, stream);
+}
+
+// First layer of an occupancy head with the second (cout -> 1, 27 offsets) folded into its epilogue, GEMM-first:
+// proj_out[k][o] = act(bias + conv(o)) . proj_w[k][:] from the fp32 accumulator row (the hidden row is never rounded to bf16 and,
+// with out_f32 == out_bf16 == NULL, never written).  proj_w is a HOST pointer ([27][cout] fp32): the weights are copied into the
+// launch's kernel parameters (constant bank) -- the one argument of the ABI that is not device memory.
+// pcg_gather_sum then forms logit[o] = bias2 + sum_k proj_out[k][nbr[k][o]].
+extern "C" int pcg_conv_fwd_tc_proj(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
+                                    const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                                    int act, float *out_f32, void *out_bf16, const float *proj_w, int proj_k, float *proj_out,
+                                    long proj_pitch, void *stream) {
+    PCG_CHECK_ARG(proj_w != nullptr && proj_out != nullptr, "pcg_conv_fwd_tc_proj: proj_w / proj_out required");
+    PCG_CHECK_ARG(proj_k == TC_PROJ_K, "pcg_conv_fwd_tc_proj: proj_k=%d must be %d (a 3x3x3 second layer)", proj_k, TC_PROJ_K);
+    PCG_CHECK_ARG(cout == 16 || cout == 32 || cout == 64, "pcg_conv_fwd_tc_proj: cout=%d must be 16, 32 or 64", cout);
+    PCG_CHECK_ARG(cin >= 17, "pcg_conv_fwd_tc_proj: cin=%d must be >= 17 (64- or 128-byte operand rows)", cin);
+    PCG_CHECK_ARG(proj_pitch >= n_out, "pcg_conv_fwd_tc_proj: proj_pitch=%ld < n_out=%ld", proj_pitch, n_out);
+    return conv_fwd_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
+                            proj_w, proj_out, proj_pitch, stream);
+}
+
+// out[o] = act(bias + sum_k planes[k][nbr[k][o]]), k ascending (one fixed-order fp32 chain per output); absent neighbours add nothing.
+// The K index loads of a thread are coalesced lines of nbr, the K plane reads land in the neighbourhood of o in every plane.
+template <int K>
+__global__ void __launch_bounds__(256) k_gather_sum(const float *__restrict__ planes, long plane_pitch, const int32_t *__restrict__ nbr,
+                                                    long nbr_pitch, long n_out, const float *__restrict__ bias, int act,
+                                                    float *__restrict__ out) {
+    const long o = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= n_out) return;
+    int idx[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) idx[k] = __ldg(nbr + (long)k * nbr_pitch + o);
+    float v[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) v[k] = idx[k] >= 0 ? __ldg(planes + (long)k * plane_pitch + idx[k]) : 0.f;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc += v[k];
+    out[o] = pcg_apply_act(acc + (bias ? __ldg(bias) : 0.f), act);
+}
+
+extern "C" int pcg_gather_sum(const float *planes, long plane_pitch, const int32_t *nbr, long nbr_pitch, int K, long n_out,
+                              const float *bias, int act, float *out, void *stream) {
+    PCG_CHECK_ARG(K == TC_PROJ_K, "pcg_gather_sum: K=%d must be %d", K, TC_PROJ_K);
+    PCG_CHECK_ARG(nbr_pitch >= n_out && plane_pitch >= 1, "pcg_gather_sum: nbr_pitch=%ld plane_pitch=%ld n_out=%ld", nbr_pitch, plane_pitch, n_out);
+    if (n_out <= 0) return 0;
+    k_gather_sum<TC_PROJ_K><<<(unsigned)cdiv(n_out, 256), 256, 0, as_stream(stream)>>>(planes, plane_pitch, nbr, nbr_pitch, n_out, bias, act, out);
+    PCG_LAUNCHED();
+    return 0;
 }

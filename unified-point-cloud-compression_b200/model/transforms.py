@@ -87,6 +87,9 @@ class SparseSynthesisTransform(nn.Module):
         first, last = head[0], head[2]
         if torch.is_grad_enabled() and x.F.requires_grad:
             return head(x)
+        if so.head_fusable(first.kernel_size, first.kernel, last.kernel_size, last.kernel):
+            o = so.occupancy_head(x.F, x.coord_set, first.kernel, first.bias, last.kernel, last.bias, packed=first._packed)
+            return ME.SparseTensor(o, _coord_set=x.coord_set)
         h = so.sparse_conv(x.F, x.coord_set, x.coord_set, first.kernel, first.bias, first.kernel_size, False,
                            act=so.ACT_RELU, packed=first._packed, out="bf16")    # hidden rows only feed the next conv
         o = so.sparse_conv(h, x.coord_set, x.coord_set, last.kernel, last.bias, last.kernel_size, False,

@@ -3,6 +3,7 @@ feature lookup.  Host-side mirror of what MinkowskiEngine's CoordinateManager + 
 do for the reference; all arithmetic happens in the CUDA kernels.
 """
 import contextlib
+import ctypes
 import os
 import weakref
 
@@ -536,6 +537,62 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
         prof.records.append(("conv_f32", (K, cin, cout), 2.0 * pairs * cin * cout,
                              4.0 * f.shape[0] * cin + 4.0 * n_out * cout, e0, e1))
     return of
+
+
+def head_fusable(ksize_a, w_a, ksize_b, w_b):
+    """Static rule for occupancy_head: conv k3 (C -> 16..64, tensor-core eligible, 64- or 128-byte operand rows), ReLU, conv k3 -> 1."""
+    if _conv_mode == "f32" or os.environ.get("PCG_HEAD_FUSED") == "0" or ksize_a != 3 or ksize_b != 3 or w_a.dim() != 3 or w_b.dim() != 3:
+        return False
+    K, cin, cmid = w_a.shape
+    return (K == 27 and tuple(w_b.shape) == (27, cmid, 1) and cmid in (16, 32, 64) and cin >= 17 and tc_eligible(K, cin, cmid)
+            and not im2col_eligible(K, cin, cmid))
+
+
+def occupancy_head(feats, cset, w_a, b_a, w_b, b_b, packed=None):
+    """logit = conv_b(relu(conv_a(x))) on one coordinate set (model/transforms.py:146-160), second layer GEMM-first:
+    the first layer's epilogue (tcgen05 kernel, thread = output row, fp32 accumulator row in registers) also forms the 27 dot
+    products s[k][p] = relu(h[p]) . w_b[k], stored offset-major; the second layer is then logit[o] = b_b + sum_k s[k][nbr[k][o]]
+    -- one 4-byte read per pair from a plane in which neighbouring outputs hit neighbouring rows, instead of a 32- to 128-byte
+    row gather per pair -- and the hidden rows are neither rounded to bf16 nor written.  Same fixed accumulation order (k ascending)."""
+    _need_cuda(feats, "features")
+    K, cin, cmid = w_a.shape
+    nbr, tmask = cset.kernel_map(cset, 3, False)
+    n = cset.n
+    dev = feats.device
+    out = torch.empty((n, 1), dtype=torch.float32, device=dev)
+    if n == 0:
+        return out
+    pitch = nbr.shape[1]
+    fb = to_bf16(feats)
+    wp = (packed or PackedWeights()).get(w_a.detach())
+    ba = b_a.reshape(-1).contiguous() if b_a is not None else None
+    bb = b_b.reshape(-1).contiguous() if b_b is not None else None
+    # the second layer's kernel travels in the launch's kernel parameters (constant bank): a host copy, made once per parameter version
+    key = (w_b.data_ptr(), w_b._version)
+    hit = getattr(packed, "_proj_host", None) if packed is not None else None
+    if hit is None or hit[0] != key:
+        hit = (key, w_b.detach().reshape(27, cmid).float().cpu().contiguous())
+        if packed is not None:
+            packed._proj_host = hit
+    w2 = hit[1]
+    planes = torch.empty((27, pitch), dtype=torch.float32, device=dev)
+    prof = profiler
+    if prof is not None:
+        pairs = prof.pairs(nbr)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+    call("pcg_conv_fwd_tc_proj", ptr(fb), fb.shape[0], cin, ptr(nbr), pitch, ptr(tmask), K, n, ptr(wp), ptr(ba), cmid,
+         ACT_RELU, None, None, ctypes.c_void_p(w2.data_ptr()), 27, ptr(planes), pitch, stream())       # w2: the one HOST pointer of the ABI
+    if prof is not None:
+        e1.record()
+    call("pcg_gather_sum", ptr(planes), pitch, ptr(nbr), pitch, 27, n, ptr(bb), ACT_NONE, ptr(out), stream())
+    if prof is not None:
+        e2.record()
+        kind = "conv_narrow" if cin <= 64 and cmid <= 16 else "conv_tc"
+        prof.records.append((kind, (K, cin, cmid), 2.0 * pairs * cin * cmid,
+                             2.0 * fb.shape[0] * cin_padded(cin) + 4.0 * 27 * n + 4.0 * K * n, e0, e1))
+        prof.records.append(("head_gather", (27, cmid, 1), 2.0 * pairs * cmid, 4.0 * 27 * n + 4.0 * K * n + 4.0 * n, e1, e2))
+    return out
 
 
 class PackedGemmWeights:
