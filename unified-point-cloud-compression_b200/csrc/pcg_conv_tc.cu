@@ -387,6 +387,13 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // PC >= 32: the second-layer weights (3.4 / 6.9 KB) are walked once per epilogue warp -- more than the constant cache keeps
+    // close (measured: 3x the issue-bound time as constant operands) -- so they are staged in shared memory once per CTA and read
+    // as broadcast 16-byte LDS; PC == 16 (1.7 KB) stays in the constant bank.
+    float *proj_sw = reinterpret_cast<float *>(ctl + 512);
+    if constexpr (PC >= 32) {
+        for (int i = tid; i < TC_PROJ_K * PC; i += 32 * (4 * T + 1)) proj_sw[i] = pw.w[i];
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -473,8 +480,19 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
                     tc_act16(p, c0, v, f);
 #pragma unroll
                     for (int k = 0; k < TC_PROJ_K; ++k) {
+                        if constexpr (PC == 16) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) ps[k] = fmaf(f[j], pw.w[k * PC + c0 + j], ps[k]);
+                            for (int j = 0; j < 16; ++j) ps[k] = fmaf(f[j], pw.w[k * PC + c0 + j], ps[k]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float4 q = *reinterpret_cast<const float4 *>(proj_sw + k * PC + c0 + 4 * j);   // warp-uniform: broadcast
+                                ps[k] = fmaf(f[4 * j], q.x, ps[k]);
+                                ps[k] = fmaf(f[4 * j + 1], q.y, ps[k]);
+                                ps[k] = fmaf(f[4 * j + 2], q.z, ps[k]);
+                                ps[k] = fmaf(f[4 * j + 3], q.w, ps[k]);
+                            }
+                        }
                         if (PC == 16 && live) p.proj_out[(long)k * p.proj_pitch + o] = ps[k];   // single column group: store as formed
                     }
                 }
@@ -673,7 +691,7 @@ static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const in
         p.stages = stages;
         p.tmem_cols = 32;
         while (p.tmem_cols < T * p.cout_p) p.tmem_cols <<= 1;
-        const size_t smem = 1024 + (size_t)stages * stage_bytes + 512;
+        const size_t smem = 1024 + (size_t)stages * stage_bytes + 512 + (proj && cout >= 32 ? (size_t)TC_PROJ_K * cout * sizeof(float) : 0);
         // tuning knobs: PCG_TC_CA bit 0 = narrow rows (RB 32 / 64), bit 1 = 128-byte rows gathered with cp.async.ca (L1-allocating);
         // PCG_TC_CARVEOUT = preferred shared-memory share of the unified L1 in percent (what is left caches the gathered rows)
         static const int ca_bits = getenv("PCG_TC_CA") ? atoi(getenv("PCG_TC_CA")) : 0;
