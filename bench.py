@@ -358,7 +358,7 @@ def main():
         traffic = json.load(open(tp))["tcgen05_conv_dram_bytes_per_step"]
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_mt / k_conv_tc + k_gemm_first (tcgen05 sparse conv kernels, all launches of one step)",
                 "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops"],
-                "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu, profiles/r01_ncu_full_v5.md)",
+                "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu --set full; source named in profiles/r01_traffic.json)",
                 "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
                 "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * depth / ms_res if ms_res else None,
                 "per": "one frame (the roofline pass codes a single frame on one stream)",

@@ -29,7 +29,7 @@ def main(path, min_us=0.0):
     print("| # | kernel | grid | " + " | ".join(lab for _, lab, _ in avail) + " |")
     print("|---|---|---|" + "---:|" * len(avail))
     for r in data:
-        name = r[idx["Kernel Name"]].split("(")[0][:28]
+        name = r[idx["Kernel Name"]].split("(")[0][:34]
         vals = []
         skip = False
         for m, lab, sc in avail:
