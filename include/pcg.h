@@ -128,14 +128,14 @@ int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const int32_t *n
 /* Occupancy head (model/transforms.py:146-160: conv k3 C -> cout, ReLU, conv k3 cout -> 1) with the second layer taken
  * GEMM-first out of the first layer's epilogue: pcg_conv_fwd_tc_proj is pcg_conv_fwd_tc (cout = 16, 32 or 64; cin >= 17)
  * that also writes proj_out[k][o] = act(bias + conv(o)) . proj_w[k][:] for the proj_k = 27 offsets of the second layer
- * (proj_w: the second layer's kernel as [27][cout] fp32 in HOST memory -- it is copied into the launch's kernel parameters so
- * that the epilogue's multiply-adds read it from the constant bank; every other pointer of this header is device memory;
- * proj_out: [27][proj_pitch] fp32, proj_pitch >= n_out), from the fp32 accumulator row; out_f32 / out_bf16 may both be NULL
- * (the hidden rows are then never written).  cout = 16, 32 or 64.
+ * (proj_w: the second layer's kernel as [27][cout] fp32, and bias_host: the FIRST layer's bias as [cout] fp32 or NULL, both in
+ * HOST memory -- they are copied into the launch's kernel parameters so that the epilogue's multiply-adds read them from the
+ * constant bank; every other pointer of this header is device memory; proj_out: [27][proj_pitch] fp32, proj_pitch >= n_out),
+ * from the fp32 accumulator row; out_f32 / out_bf16 may both be NULL (the hidden rows are then never written).  cout = 16, 32 or 64.
  * pcg_gather_sum finishes the second layer on the same 3x3x3 neighbour table: out[o] = act(bias[0] + sum_k planes[k][nbr[k][o]]),
- * k ascending, absent neighbours skipped (K must be 27). */
+ * k ascending, absent neighbours skipped (K must be 27; bias: device pointer or NULL). */
 int pcg_conv_fwd_tc_proj(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                         const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                         const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias_host, int cout,
                          int act, float *out_f32, void *out_bf16, const float *proj_w, int proj_k, float *proj_out,
                          long proj_pitch, void *stream);
 int pcg_gather_sum(const float *planes, long plane_pitch, const int32_t *nbr, long nbr_pitch, int K, long n_out,

@@ -51,9 +51,15 @@ struct TcParams {
 // Second-layer weights [TC_PROJ_K][PC] of the fused head, passed BY VALUE as a kernel parameter: they sit in the constant bank, so
 // every FFMA of the epilogue projection takes its weight as a constant operand (no load instruction, no latency).
 // 27 x 64 x 4 B = 6.9 KB (kernel parameters may be up to 32 KB since CUDA 12.1).  PC = 0: no projection (empty).
+// Layout: offset PAIRS, column-major: w2[c * TC_PROJ_KP + kp] = {w[2 kp][c], w[2 kp + 1][c]} (offset 27 = zero), so that one packed
+// fp32 multiply-add (fma.rn.f32x2, sm_100) advances two offsets and consecutive instructions feed DIFFERENT accumulators (14
+// independent chains per column instead of one 16-deep dependent chain per offset).  bias: the first layer's bias, also as constant
+// operands (the ncu source view of the first version showed a third of the projection's stall samples on the bias LDGs).
+#define TC_PROJ_KP ((TC_PROJ_K + 1) / 2)
 template <int PC>
 struct TcProjW {
-    float w[TC_PROJ_K * PC];
+    float2 w2[TC_PROJ_KP * PC];
+    float bias[PC];
 };
 template <>
 struct TcProjW<0> {
@@ -90,11 +96,24 @@ __device__ __forceinline__ void tc_store16(const TcParams &p, long o, int c0, co
     }
 }
 
-// the same 16 columns after bias + activation, kept in registers (fused second head layer)
-__device__ __forceinline__ void tc_act16(const TcParams &p, int c0, const uint32_t (&v)[16], float (&f)[16]) {
+// 16 already activated columns of row o -> fp32 and/or bf16 rows (cout % 16 == 0)
+__device__ __forceinline__ void tc_write16(const TcParams &p, long o, int c0, const float (&f)[16]) {
+    if (p.out_f32) {
+        float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + o * p.cout + c0);
 #pragma unroll
-    for (int j = 0; j < 16; ++j)
-        f[j] = pcg_apply_act(__uint_as_float(v[j]) + ((p.bias && c0 + j < p.cout) ? __ldg(p.bias + c0 + j) : 0.f), p.act);
+        for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+    }
+    if (p.out_bf16) {
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+            pk[j] = *reinterpret_cast<uint32_t *>(&h);
+        }
+        uint4 *dst = reinterpret_cast<uint4 *>(p.out_bf16 + o * p.cout + c0);
+        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
 }
 
 // LSU gather of one 128-row x 128-byte operand sub-tile into its 128B-swizzled image at dst_tile.  Lane m holds the neighbour
@@ -330,7 +349,7 @@ __global__ void __launch_bounds__(160) k_conv_tc(const __grid_constant__ CUtenso
 // on the 27x128x64 layer; the gather4 row rate, ~4 cycles per row per SM, paces the pair.)
 // PC: 0 = plain; 16 / 32 / 64 = cout of a first head layer whose second layer (cout -> 1, 27 offsets) is folded into the epilogue.
 template <int T, int RB, bool CA, int PC = 0>
-__global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams p, const TcProjW<PC> pw) {
+__global__ void __launch_bounds__(32 * (4 * T + 1), (T == 2 && PC != 0) ? 2 : 0) k_conv_tc_mt(const TcParams p, const TcProjW<PC> pw) {   // T = 2 runs two CTAs per SM: the projection must stay <= 112 registers
     constexpr int MMA_WARP = 4 * T;
     constexpr uint32_t A_BYTES = TC_ROWS * RB;         // one gathered operand sub-tile (RB = 128 / 64 / 32-byte rows: cin_p >= 64 / 32 / 16)
     extern __shared__ uint8_t smem_raw[];
@@ -390,9 +409,9 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
     // PC >= 32: the second-layer weights (3.4 / 6.9 KB) are walked once per epilogue warp -- more than the constant cache keeps
     // close (measured: 3x the issue-bound time as constant operands) -- so they are staged in shared memory once per CTA and read
     // as broadcast 16-byte LDS; PC == 16 (1.7 KB) stays in the constant bank.
-    float *proj_sw = reinterpret_cast<float *>(ctl + 512);
+    float2 *proj_sw = reinterpret_cast<float2 *>(ctl + 512);
     if constexpr (PC >= 32) {
-        for (int i = tid; i < TC_PROJ_K * PC; i += 32 * (4 * T + 1)) proj_sw[i] = pw.w[i];
+        for (int i = tid; i < TC_PROJ_KP * PC; i += 32 * (4 * T + 1)) proj_sw[i] = pw.w2[i];      // column-major pairs, as in the parameter
     }
     tc_fence_before();
     __syncthreads();
@@ -463,10 +482,11 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
                     if (live) tc_store16(p, o, c0, v);
                 }
             } else {
-                // fused second layer: ps[k] = act(row) . w2[k][:], columns ascending (one fixed fp32 chain per offset)
-                float ps[TC_PROJ_K];
+                // fused second layer: ps[k] = act(row) . w2[k][:], columns ascending (one fixed fp32 chain per offset; the packed
+                // multiply-add rounds each half like a scalar fma.rn, so pairing offsets does not change a bit)
+                float2 ps2[TC_PROJ_KP];
 #pragma unroll
-                for (int k = 0; k < TC_PROJ_K; ++k) ps[k] = 0.f;
+                for (int kp = 0; kp < TC_PROJ_KP; ++kp) ps2[kp] = make_float2(0.f, 0.f);
 #pragma unroll
                 for (int c0 = 0; c0 < PC; c0 += 16) {
                     uint32_t v[16];
@@ -475,30 +495,32 @@ __global__ void __launch_bounds__(32 * (4 * T + 1)) k_conv_tc_mt(const TcParams 
 #pragma unroll
                         for (int j = 0; j < 16; ++j) v[j] = 0u;
                     }
-                    if (live) tc_store16(p, o, c0, v);
                     float f[16];
-                    tc_act16(p, c0, v, f);
 #pragma unroll
-                    for (int k = 0; k < TC_PROJ_K; ++k) {
+                    for (int j = 0; j < 16; ++j) f[j] = pcg_apply_act(__uint_as_float(v[j]) + pw.bias[c0 + j], p.act);
+                    if (live && (p.out_f32 || p.out_bf16)) tc_write16(p, o, c0, f);     // the hidden row, only if a caller wants it
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float2 ff = make_float2(f[j], f[j]);
                         if constexpr (PC == 16) {
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) ps[k] = fmaf(f[j], pw.w[k * PC + c0 + j], ps[k]);
+                            for (int kp = 0; kp < TC_PROJ_KP; ++kp) ps2[kp] = __ffma2_rn(ff, pw.w2[(c0 + j) * TC_PROJ_KP + kp], ps2[kp]);
                         } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const float4 q = *reinterpret_cast<const float4 *>(proj_sw + k * PC + c0 + 4 * j);   // warp-uniform: broadcast
-                                ps[k] = fmaf(f[4 * j], q.x, ps[k]);
-                                ps[k] = fmaf(f[4 * j + 1], q.y, ps[k]);
-                                ps[k] = fmaf(f[4 * j + 2], q.z, ps[k]);
-                                ps[k] = fmaf(f[4 * j + 3], q.w, ps[k]);
+                            for (int kp = 0; kp < TC_PROJ_KP; kp += 2) {
+                                const float4 q = *reinterpret_cast<const float4 *>(proj_sw + (c0 + j) * TC_PROJ_KP + kp);   // warp-uniform: broadcast
+                                ps2[kp] = __ffma2_rn(ff, make_float2(q.x, q.y), ps2[kp]);
+                                ps2[kp + 1] = __ffma2_rn(ff, make_float2(q.z, q.w), ps2[kp + 1]);
                             }
                         }
-                        if (PC == 16 && live) p.proj_out[(long)k * p.proj_pitch + o] = ps[k];   // single column group: store as formed
                     }
                 }
-                if (PC != 16 && live) {
+                if (live) {                                          // lane = row: one coalesced 128-byte store per warp and offset
 #pragma unroll
-                    for (int k = 0; k < TC_PROJ_K; ++k) p.proj_out[(long)k * p.proj_pitch + o] = ps[k];   // lane = row: coalesced
+                    for (int kp = 0; kp < TC_PROJ_KP; ++kp) {
+                        p.proj_out[(long)(2 * kp) * p.proj_pitch + o] = ps2[kp].x;
+                        if (2 * kp + 1 < TC_PROJ_K) p.proj_out[(long)(2 * kp + 1) * p.proj_pitch + o] = ps2[kp].y;
+                    }
                 }
             }
         }
@@ -625,8 +647,8 @@ static int launch_tc(const CUtensorMap &tm, const TcParams &p, size_t smem, cuda
 
 static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
                             const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
-                            int act, float *out_f32, void *out_bf16, const float *proj_w_host, float *proj_out, long proj_pitch,
-                            void *stream) {
+                            int act, float *out_f32, void *out_bf16, const float *proj_w_host, const float *bias_host, float *proj_out,
+                            long proj_pitch, void *stream) {
     PCG_CHECK_ARG(cin >= 1 && cin <= 1024, "pcg_conv_fwd_tc: cin=%d", cin);
     PCG_CHECK_ARG(cout >= 1 && cout <= 256, "pcg_conv_fwd_tc: cout=%d must be in [1,256]", cout);
     PCG_CHECK_ARG(out_bf16 == nullptr || (cout & 15) == 0, "pcg_conv_fwd_tc: a bf16 output needs cout %% 16 == 0 (cout=%d)", cout);
@@ -691,7 +713,7 @@ static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const in
         p.stages = stages;
         p.tmem_cols = 32;
         while (p.tmem_cols < T * p.cout_p) p.tmem_cols <<= 1;
-        const size_t smem = 1024 + (size_t)stages * stage_bytes + 512 + (proj && cout >= 32 ? (size_t)TC_PROJ_K * cout * sizeof(float) : 0);
+        const size_t smem = 1024 + (size_t)stages * stage_bytes + 512 + (proj && cout >= 32 ? (size_t)TC_PROJ_KP * cout * sizeof(float2) : 0);
         // tuning knobs: PCG_TC_CA bit 0 = narrow rows (RB 32 / 64), bit 1 = 128-byte rows gathered with cp.async.ca (L1-allocating);
         // PCG_TC_CARVEOUT = preferred shared-memory share of the unified L1 in percent (what is left caches the gathered rows)
         static const int ca_bits = getenv("PCG_TC_CA") ? atoi(getenv("PCG_TC_CA")) : 0;
@@ -712,7 +734,11 @@ static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const in
 #define PCG_MTP(TT, RBB, PCC)                                                                                             \
     do {                                                                                                                  \
         TcProjW<PCC> pw;                                                                                                  \
-        memcpy(pw.w, proj_w_host, sizeof(pw.w));                                                                          \
+        for (int kp = 0; kp < TC_PROJ_KP; ++kp)                                                                           \
+            for (int c = 0; c < PCC; ++c)                                                                                 \
+                pw.w2[c * TC_PROJ_KP + kp] = make_float2(proj_w_host[(2 * kp) * PCC + c],                                 \
+                                                         2 * kp + 1 < TC_PROJ_K ? proj_w_host[(2 * kp + 1) * PCC + c] : 0.f); \
+        for (int c = 0; c < PCC; ++c) pw.bias[c] = bias_host ? bias_host[c] : 0.f;                                        \
         PCG_CUDA(cudaFuncSetAttribute(k_conv_tc_mt<TT, RBB, false, PCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         k_conv_tc_mt<TT, RBB, false, PCC><<<(unsigned)cdiv(tiles, TT), 32 * (4 * TT + 1), smem, st>>>(p, pw);             \
     } while (0)
@@ -757,16 +783,16 @@ extern "C" int pcg_conv_fwd_tc(const void *feats_bf16, long n_in, int cin, const
                                const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
                                int act, float *out_f32, void *out_bf16, void *stream) {
     return conv_fwd_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
-                            nullptr, nullptr, 0, stream);
+                            nullptr, nullptr, nullptr, 0, stream);
 }
 
 // First layer of an occupancy head with the second (cout -> 1, 27 offsets) folded into its epilogue, GEMM-first:
 // proj_out[k][o] = act(bias + conv(o)) . proj_w[k][:] from the fp32 accumulator row (the hidden row is never rounded to bf16 and,
-// with out_f32 == out_bf16 == NULL, never written).  proj_w is a HOST pointer ([27][cout] fp32): the weights are copied into the
-// launch's kernel parameters (constant bank) -- the one argument of the ABI that is not device memory.
+// with out_f32 == out_bf16 == NULL, never written).  proj_w ([27][cout] fp32) and bias_host ([cout] fp32 or NULL) are HOST pointers:
+// they are copied into the launch's kernel parameters (constant bank) -- the only arguments of the ABI that are not device memory.
 // pcg_gather_sum then forms logit[o] = bias2 + sum_k proj_out[k][nbr[k][o]].
 extern "C" int pcg_conv_fwd_tc_proj(const void *feats_bf16, long n_in, int cin, const int32_t *nbr, long nbr_pitch,
-                                    const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias, int cout,
+                                    const uint32_t *tile_mask, int K, long n_out, const void *wpacked, const float *bias_host, int cout,
                                     int act, float *out_f32, void *out_bf16, const float *proj_w, int proj_k, float *proj_out,
                                     long proj_pitch, void *stream) {
     PCG_CHECK_ARG(proj_w != nullptr && proj_out != nullptr, "pcg_conv_fwd_tc_proj: proj_w / proj_out required");
@@ -774,8 +800,8 @@ extern "C" int pcg_conv_fwd_tc_proj(const void *feats_bf16, long n_in, int cin, 
     PCG_CHECK_ARG(cout == 16 || cout == 32 || cout == 64, "pcg_conv_fwd_tc_proj: cout=%d must be 16, 32 or 64", cout);
     PCG_CHECK_ARG(cin >= 17, "pcg_conv_fwd_tc_proj: cin=%d must be >= 17 (64- or 128-byte operand rows)", cin);
     PCG_CHECK_ARG(proj_pitch >= n_out, "pcg_conv_fwd_tc_proj: proj_pitch=%ld < n_out=%ld", proj_pitch, n_out);
-    return conv_fwd_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, bias, cout, act, out_f32, out_bf16,
-                            proj_w, proj_out, proj_pitch, stream);
+    return conv_fwd_tc_impl(feats_bf16, n_in, cin, nbr, nbr_pitch, tile_mask, K, n_out, wpacked, nullptr, cout, act, out_f32, out_bf16,
+                            proj_w, bias_host, proj_out, proj_pitch, stream);
 }
 
 // out[o] = act(bias + sum_k planes[k][nbr[k][o]]), k ascending (one fixed-order fp32 chain per output); absent neighbours add nothing.

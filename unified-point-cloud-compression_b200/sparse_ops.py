@@ -565,24 +565,26 @@ def occupancy_head(feats, cset, w_a, b_a, w_b, b_b, packed=None):
     pitch = nbr.shape[1]
     fb = to_bf16(feats)
     wp = (packed or PackedWeights()).get(w_a.detach())
-    ba = b_a.reshape(-1).contiguous() if b_a is not None else None
     bb = b_b.reshape(-1).contiguous() if b_b is not None else None
-    # the second layer's kernel travels in the launch's kernel parameters (constant bank): a host copy, made once per parameter version
-    key = (w_b.data_ptr(), w_b._version)
+    # the second layer's kernel and the first layer's bias travel in the launch's kernel parameters (constant bank): host copies,
+    # made once per parameter version
+    key = (w_b.data_ptr(), w_b._version, None if b_a is None else (b_a.data_ptr(), b_a._version))
     hit = getattr(packed, "_proj_host", None) if packed is not None else None
     if hit is None or hit[0] != key:
-        hit = (key, w_b.detach().reshape(27, cmid).float().cpu().contiguous())
+        hit = (key, w_b.detach().reshape(27, cmid).float().cpu().contiguous(),
+               None if b_a is None else b_a.detach().reshape(-1).float().cpu().contiguous())
         if packed is not None:
             packed._proj_host = hit
-    w2 = hit[1]
+    w2, ba_host = hit[1], hit[2]
     planes = torch.empty((27, pitch), dtype=torch.float32, device=dev)
     prof = profiler
     if prof is not None:
         pairs = prof.pairs(nbr)
         e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         e0.record()
-    call("pcg_conv_fwd_tc_proj", ptr(fb), fb.shape[0], cin, ptr(nbr), pitch, ptr(tmask), K, n, ptr(wp), ptr(ba), cmid,
-         ACT_RELU, None, None, ctypes.c_void_p(w2.data_ptr()), 27, ptr(planes), pitch, stream())       # w2: the one HOST pointer of the ABI
+    call("pcg_conv_fwd_tc_proj", ptr(fb), fb.shape[0], cin, ptr(nbr), pitch, ptr(tmask), K, n, ptr(wp),
+         None if ba_host is None else ctypes.c_void_p(ba_host.data_ptr()), cmid,
+         ACT_RELU, None, None, ctypes.c_void_p(w2.data_ptr()), 27, ptr(planes), pitch, stream())       # w2 / bias: the HOST pointers of the ABI
     if prof is not None:
         e1.record()
     call("pcg_gather_sum", ptr(planes), pitch, ptr(nbr), pitch, 27, n, ptr(bb), ACT_NONE, ptr(out), stream())
