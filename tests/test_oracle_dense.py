@@ -115,3 +115,38 @@ def test_sparse_tensor_dedupes_keeping_first():
     assert x.C.tolist() == [[0, 1, 1, 1], [0, 2, 2, 2]] and x.F[:, 0].tolist() == [1.0, 2.0]
     c, f = me_ref.sparse_quantize(torch.tensor([[0, 1.7, 1.2, 1.9], [0, 1.1, 1.0, 1.5]]), torch.tensor([[1.0], [2.0]]), quantization_size=1.0)
     assert c.tolist() == [[0, 1, 1, 1]] and f.tolist() == [[1.0]]
+
+
+def test_head_second_layer_gemm_first_identity():
+    """The occupancy head's second layer taken GEMM-first (sparse_ops.occupancy_head: s[k][p] = relu(h[p]) . w2[k] in the first layer's
+    epilogue, then logit[o] = b2 + sum_k s[k][nbr[k][o]], offsets ascending) is the same function as conv(relu(conv(x)))
+    (model/transforms.py:146-160): checked here on the CPU oracle, with integer operands bit for bit."""
+    pts, _ = synth.small_cloud(seed=5)
+    C = np.concatenate([np.zeros((len(pts), 1), np.int32), pts], axis=1)
+    n = len(C)
+    nbr = native.kernel_map(C, C, 3, 1, False)                      # [27][n], -1 where absent
+    rng = np.random.default_rng(11)
+    for integer in (False, True):
+        if integer:
+            X = rng.integers(-2, 3, (n, 32)).astype(np.float32)
+            W1 = rng.integers(-1, 2, (27, 32, 16)).astype(np.float32)
+            W2 = rng.integers(-1, 2, (27, 16, 1)).astype(np.float32)
+            b1 = rng.integers(-3, 4, (1, 16)).astype(np.float32)
+        else:
+            X = rng.standard_normal((n, 32)).astype(np.float32)
+            W1 = (rng.standard_normal((27, 32, 16)) * 0.1).astype(np.float32)
+            W2 = (rng.standard_normal((27, 16, 1)) * 0.1).astype(np.float32)
+            b1 = (rng.standard_normal((1, 16)) * 0.1).astype(np.float32)
+        b2 = np.full((1, 1), 1.0, np.float32)
+        h = native.conv(X, nbr, W1, b1, 1)                          # first layer + ReLU
+        ref = native.conv(h, nbr, W2, b2, 0)[:, 0]
+        planes = (h @ W2[:, :, 0].T).T.astype(np.float32)           # s[k][p]
+        acc = np.zeros(n, np.float32)
+        for k in range(27):
+            idx = nbr[k][:n]
+            acc += np.where(idx >= 0, planes[k][np.maximum(idx, 0)], 0.0).astype(np.float32)
+        mine = acc + b2[0, 0]
+        if integer:
+            assert np.array_equal(mine, ref)
+        else:
+            assert np.abs(mine - ref).max() <= 1e-5 * max(1.0, np.abs(ref).max())
