@@ -544,8 +544,9 @@ def head_fusable(ksize_a, w_a, ksize_b, w_b):
     if _conv_mode == "f32" or os.environ.get("PCG_HEAD_FUSED") == "0" or ksize_a != 3 or ksize_b != 3 or w_a.dim() != 3 or w_b.dim() != 3:
         return False
     K, cin, cmid = w_a.shape
-    return (K == 27 and tuple(w_b.shape) == (27, cmid, 1) and cmid in (16, 32, 64) and cin >= 17 and tc_eligible(K, cin, cmid)
-            and not im2col_eligible(K, cin, cmid))
+    # (64-byte operand rows, 17 <= cin <= 32, are covered by the parity tests with cmid = 16 only: wider hidden rows on them stay unfused)
+    return (K == 27 and tuple(w_b.shape) == (27, cmid, 1) and cmid in (16, 32, 64) and (cin >= 33 or (cin >= 17 and cmid == 16))
+            and tc_eligible(K, cin, cmid) and not im2col_eligible(K, cin, cmid))
 
 
 def occupancy_head(feats, cset, w_a, b_a, w_b, b_b, packed=None):
