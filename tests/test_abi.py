@@ -61,3 +61,23 @@ def test_reference_state_dict_loads_into_product_mirror():
     assert torch.equal(net.entropy_model.gaussian_conditional._quantized_cdf, sd["entropy_model.gaussian_conditional._quantized_cdf"])
     assert torch.equal(net.entropy_model.entropy_bottleneck._quantized_cdf, sd["entropy_model.entropy_bottleneck._quantized_cdf"])
     assert torch.equal(net.entropy_model.entropy_bottleneck._offset, sd["entropy_model.entropy_bottleneck._offset"])
+
+
+def test_static_kernel_selection_rules_cover_the_reference_heads():
+    """Host logic: the occupancy heads of the reference configurations (model/transforms.py:146-160 with N = 128: 128->64->1 twice,
+    32->16->1) take the fused GEMM-first path; the rule is static (shapes and conv mode only -- never timing),
+    switches off in fp32 parity mode, and shapes outside the tested set stay on the two-convolution path."""
+    import torch
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    so = pkg.sparse_ops
+    fus = lambda cin, cmid, k1=3, k2=3: so.head_fusable(k1, torch.zeros(k1 ** 3, cin, cmid), k2, torch.zeros(k2 ** 3, cmid, 1))
+    assert fus(128, 64) and fus(32, 16) and fus(64, 32)
+    assert not fus(16, 8) and not fus(8, 4) and not fus(32, 32) and not fus(128, 128)
+    assert not fus(128, 64, k1=5) and not so.head_fusable(3, torch.zeros(27, 128, 64), 3, torch.zeros(27, 64, 2))
+    prev = so.set_conv_mode("f32")
+    try:
+        assert not fus(128, 64)
+    finally:
+        so.set_conv_mode(prev)
+    assert so.tc_eligible(27, 128, 64) and so.tc_eligible(125, 128, 128) and not so.tc_eligible(1, 32, 3)
+    assert so.cells_eligible(5, 2, 128, 128) and so.cells_eligible(5, 2, 128, 32) and not so.cells_eligible(2, 2, 192, 192)
