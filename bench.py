@@ -204,7 +204,7 @@ def main():
     host_clouds = [torch.from_numpy(np.concatenate([p.astype(np.float32), c], axis=1)).pin_memory() for p, c in frames]
     dev_clouds = [h.to(dev) for h in host_clouds]
     codec_mod = importlib.import_module(pkg.__name__ + ".codec")
-    pipe = codec_mod.FramePipeline(dev, depth) if depth > 1 else None
+    pipe = codec_mod.FramePipeline(dev, depth, model=net) if depth > 1 else None
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
     def step_resident(j=0):

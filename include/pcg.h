@@ -18,7 +18,10 @@
  *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
  *   - return value 0 = ok, non-zero = error; pcg_last_error() gives a thread-local message;
  *   - coordinates are rows of 4 x int32 (batch, x, y, z), 16-byte aligned, with
- *     batch in [0, 32767] and x,y,z in [-32768, 32767] (they are packed into one 64-bit key);
+ *     batch in [0, 32767] and x,y,z in [-32768, 32767] (they are packed into one 64-bit key).
+ *     MinkowskiEngine takes any int32; here a row outside that range is NOT inserted and bit 2
+ *     (value 2) of the call's `d_status` word is raised, which the host layer turns into an error
+ *     (a wrapped key would silently merge two voxels);
  *   - features are row-major fp32 (N x C) unless a bf16 shadow is named;
  *   - kernel offsets follow MinkowskiEngine: odd k -> {-(k/2)..k/2}, even k -> {0..k-1},
  *     offset index i = ix + k*iy + k*k*iz;
@@ -50,8 +53,10 @@ long pcg_nbr_pitch(long n_out);                 /* row pitch (elements) of a nei
 size_t pcg_scratch_bytes(long n_items);         /* scratch needed by any compaction/select over n_items */
 
 /* ---- coordinate hash: replaces ME CoordinateMapGPU::insert_and_map (ME1) -------------------
- * keys: uint64[cap], vals: int32[cap].  After build, lookup(c) = smallest row with coordinate c. */
-int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, void *stream);
+ * keys: uint64[cap], vals: int32[cap].  After build, lookup(c) = smallest row with coordinate c.
+ * d_status (optional int32 word): OR-ed with 2 when a row lies outside the packing range; this call never clears it
+ * (a caller may keep one sticky word per stream and read it at its next synchronisation point). */
+int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, int32_t *d_status, void *stream);
 int pcg_hash_lookup(const uint64_t *keys, const int32_t *vals, long cap, const int32_t *query, long nq,
                     int32_t *rows_out, void *stream);
 
@@ -59,15 +64,15 @@ int pcg_hash_lookup(const uint64_t *keys, const int32_t *vals, long cap, const i
  * out_coords: up to n rows; out_index: source row of every kept row; table ends up mapping
  * unique coordinate -> new row. */
 int pcg_unique_first(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap,
-                     int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
-                     size_t scratch_bytes, void *stream);
+                     int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, int32_t *d_status, void *scratch,
+                     size_t scratch_bytes, void *stream);    /* d_status (optional): cleared, then 2 = row out of range */
 
 /* Strided output coordinates floor(c/step)*step, first-occurrence order, + their hash table
  * (ME CoordinateMapGPU::stride; used by every stride-2 MinkowskiConvolution and by
  * transforms.py:166 down_conv whose output coordinates alone are consumed, a6). */
 int pcg_stride_coords(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
-                      int32_t *out_coords, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
-                      void *stream);
+                      int32_t *out_coords, int32_t *d_n_out, int32_t *d_status, void *scratch, size_t scratch_bytes,
+                      void *stream);                         /* d_status (optional): cleared, then 2 = row out of range */
 
 /* Generative up-sampling coordinates unique{p + off_i*ts_out} over all rows and all ksize^3
  * offsets + their hash table.  Row order: first occurrence in an enumeration that groups the offsets by

@@ -97,7 +97,8 @@ def pmf_to_quantized_cdf(pmf, precision=16):
         raise ValueError("Invalid `pmf`, non-finite or negative element found")
     cdf = np.zeros(len(pmf) + 1, dtype=np.uint64)
     # std::round on float: half away from zero
-    cdf[1:] = np.floor(pmf.astype(np.float32) * np.float32(1 << precision) + np.float32(0.5)).astype(np.uint64)
+    # (the fp32 product widened to double before the +0.5: in fp32 the addition itself rounds, 0.49999997 + 0.5 -> 1.0)
+    cdf[1:] = np.floor((pmf.astype(np.float32) * np.float32(1 << precision)).astype(np.float64) + 0.5).astype(np.uint64)
     total = int(cdf.sum())
     if total == 0:
         raise ValueError("Invalid `pmf`: at least one element must have a non-zero probability.")

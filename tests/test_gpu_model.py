@@ -211,7 +211,7 @@ def test_frames_in_flight_reproduce_single_stream_results(pkg, dev):
     with torch.no_grad():
         ref = [code(c) for c in clouds]
         torch.cuda.synchronize()
-        pipe = codec.FramePipeline(dev, depth=3)
+        pipe = codec.FramePipeline(dev, depth=3, model=net)
         try:
             for _ in range(2):
                 got = pipe.map(code, clouds)

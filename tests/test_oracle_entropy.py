@@ -109,6 +109,19 @@ def test_product_host_coder_is_byte_identical_to_oracle():
         assert (hc.pmf_to_quantized_cdf(np.array(pmf, np.float32)) == cai_ref.pmf_to_quantized_cdf(np.array(pmf, np.float32))).all()
 
 
+def test_pmf_to_cdf_rounds_like_std_round():
+    """compressai rounds p * 2^16 with std::round; adding 0.5 in fp32 instead rounds 0.49999997 up to 1."""
+    pkg = importlib.import_module("unified-point-cloud-compression_b200")
+    hc = importlib.import_module(pkg.__name__ + ".host_coder")
+    edge = np.float32(np.nextafter(np.float32(0.5), np.float32(0.0))) / np.float32(65536.0)     # p * 65536 == 0.49999997f exactly
+    assert np.float32(edge * np.float32(65536.0)) + np.float32(0.5) == np.float32(1.0)            # the fp32 addition rounds up
+    pmf = np.array([0.25, edge, 0.75], np.float32)
+    # frequencies before renormalisation must be [16384, 0, 49152]: the zero then takes one count from the cheapest donor
+    for fn in (cai_ref.pmf_to_quantized_cdf, hc.pmf_to_quantized_cdf):
+        cdf = fn(pmf)
+        assert list(np.diff(cdf)) == [16383, 1, 49152], list(np.diff(cdf))
+
+
 def test_product_entropy_tables_match_oracle():
     """Same parameters -> same 16-bit CDF tables (they define cdf_length / offset, hence the bitstream)."""
     pkg = importlib.import_module("unified-point-cloud-compression_b200")

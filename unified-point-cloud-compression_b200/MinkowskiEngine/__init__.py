@@ -141,6 +141,20 @@ class MinkowskiConvolutionBase(nn.Module):
             if self.bias is not None:
                 self.bias.uniform_(-stdv, stdv)
 
+    def prepare(self):
+        """Pack the operand images the static kernel-selection rules will ask for (sparse_ops.pack_kind) before the first
+        frame, so that concurrent frames (codec.FramePipeline) only ever read these caches."""
+        w3 = self.kernel.detach() if self.kernel.dim() == 3 else self.kernel.detach().unsqueeze(0)
+        if not w3.is_cuda:
+            return
+        K, cin, cout = w3.shape
+        if self.is_transpose and self.expand_coordinates and so.cells_eligible(self.kernel_size, self.stride, cin, cout):
+            self._packed_gemm.get(w3)
+            return
+        kind = so.pack_kind(K, cin, cout, fp32_input=cin <= 8)
+        if kind is not None:
+            self._packed.get(w3, kind=kind)
+
     def forward(self, input, coordinates=None, _act=None):
         # _act: activation fused into the epilogue for THIS call (passed as an argument, not kept on the module: several
         # frames may run through the same module concurrently, codec.FramePipeline)

@@ -24,10 +24,10 @@ _PROTOS = {
     "pcg_tc_cin_padded": (_I, [_I]),
     "pcg_tc_set_mt_min_tiles": (_L, [_L]),
     "pcg_scratch_bytes": (_SZ, [_L]),
-    "pcg_hash_build": (_I, [_P, _L, _P, _P, _L, _P]),
+    "pcg_hash_build": (_I, [_P, _L, _P, _P, _L, _P, _P]),
     "pcg_hash_lookup": (_I, [_P, _P, _L, _P, _L, _P, _P]),
-    "pcg_unique_first": (_I, [_P, _L, _P, _P, _L, _P, _P, _P, _P, _SZ, _P]),
-    "pcg_stride_coords": (_I, [_P, _L, _I, _P, _P, _L, _P, _P, _P, _SZ, _P]),
+    "pcg_unique_first": (_I, [_P, _L, _P, _P, _L, _P, _P, _P, _P, _P, _SZ, _P]),
+    "pcg_stride_coords": (_I, [_P, _L, _I, _P, _P, _L, _P, _P, _P, _P, _SZ, _P]),
     "pcg_generate_coords": (_I, [_P, _L, _I, _I, _I, _P, _P, _L, _P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _L, _P, _P]),
     "pcg_sort_rows": (_I, [_P, _L, _I, _P, _P, _SZ, _P]),

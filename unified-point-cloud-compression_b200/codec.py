@@ -67,6 +67,23 @@ class StreamCodec:
         return gather_results(local, self.world, self.rank)
 
 
+def record_stream(obj, stream):
+    """`tensor.record_stream(stream)` on every CUDA tensor reachable from a worker's result (tensors, lists / tuples / dicts of
+    them, SparseTensor-like objects with `.F` / `.C`): the consumer's stream now also owns the blocks."""
+    if torch.is_tensor(obj):
+        if obj.is_cuda:
+            obj.record_stream(stream)
+    elif isinstance(obj, (list, tuple)):
+        for o in obj:
+            record_stream(o, stream)
+    elif isinstance(obj, dict):
+        for o in obj.values():
+            record_stream(o, stream)
+    elif hasattr(obj, "F") and hasattr(obj, "C"):
+        record_stream(obj.F, stream)
+        record_stream(obj.C, stream)
+
+
 class FramePipeline:
     """Several frames in flight on ONE GPU: `depth` host threads, each with its own CUDA stream.
 
@@ -74,16 +91,21 @@ class FramePipeline:
     from the device: ~18 stream synchronisations per frame), so a single stream leaves the GPU idle for ~10 % of a
     frame while the host wakes up and enqueues again.  Frames are independent (intra-only codec), so a second frame on
     another stream fills those gaps; the ctypes calls into libpcg.so, torch's launches and `.item()` all release the
-    GIL.  Every worker owns its scratch workspace (sparse_ops.scratch is keyed by stream) and its tensors; the model
-    parameters and packed weights are read-only after warm-up.  No data-path collective, no cross-stream dependency
-    other than the optional `after` event of `submit`.
+    GIL.  Every worker owns its scratch workspace (sparse_ops.scratch is keyed by stream) and its tensors.  The caches the
+    workers share -- packed weights, packed prior parameters, host CDF tables -- are filled by `model.prepare()` here, before
+    any worker starts, and a later miss (a parameter changed) is taken under a lock with the packing stream synchronised
+    before the buffer is published (sparse_ops.pack_lock).  Tensors handed back to the caller are `record_stream`-ed on the
+    caller's stream, so the caching allocator does not recycle their blocks on the worker stream while the caller still
+    reads them.  No data-path collective, no cross-stream dependency other than the optional `after` event of `submit`.
     """
 
-    def __init__(self, device, depth=2):
+    def __init__(self, device, depth=2, model=None):
         import queue
         import threading
         self.device = torch.device(device)
         self.depth = int(depth)
+        if model is not None:
+            model.prepare()
         self._jobs = queue.Queue()
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.depth)]
         self._threads = [threading.Thread(target=self._work, args=(s,), daemon=True) for s in self.streams]
@@ -110,7 +132,8 @@ class FramePipeline:
 
     def submit(self, fn, *args, after=None):
         """Run fn(*args) on the next free worker (its stream current, no_grad).  `after`: a CUDA event the worker's
-        stream waits for first.  Returns a Future of (result, CUDA event recorded when the worker's launches end)."""
+        stream waits for first.  Returns a Future of (result, CUDA event recorded when the worker's launches end); a caller
+        that consumes the result on another stream waits for the event and calls `record_stream(result, that_stream)`."""
         from concurrent.futures import Future
         fut = Future()
         self._jobs.put((fn, args, after, fut))
@@ -120,9 +143,11 @@ class FramePipeline:
         """fn(item) for every item, `depth` at a time; results in order.  The calling stream waits for all of them."""
         futs = [self.submit(fn, it, after=after) for it in items]
         out = []
+        cur = torch.cuda.current_stream(self.device)
         for f in futs:
             res, done = f.result()
-            torch.cuda.current_stream(self.device).wait_event(done)
+            cur.wait_event(done)
+            record_stream(res, cur)
             out.append(res)
         return out
 

@@ -16,6 +16,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import entropy_ops as eo
+from .. import sparse_ops as so
 from .. import host_coder
 from .ops.bound_ops import LowerBound
 
@@ -121,11 +122,13 @@ class EntropyModel(nn.Module):
     def _tables(self):
         self._check_cdf_size(); self._check_cdf_length(); self._check_offsets_size()
         key = (self._quantized_cdf.data_ptr(), self._quantized_cdf._version)
-        if self._host_tables is None or self._host_tables[0] != key:
-            self._host_tables = (key, self._quantized_cdf.cpu().numpy().astype(np.int32),
-                                 self._cdf_length.reshape(-1).cpu().numpy().astype(np.int32),
-                                 self._offset.reshape(-1).cpu().numpy().astype(np.int32))
-        return self._host_tables[1:]
+        hit = self._host_tables                      # one tuple, published whole (several frames may run concurrently)
+        if hit is None or hit[0] != key:
+            hit = (key, self._quantized_cdf.cpu().numpy().astype(np.int32),
+                   self._cdf_length.reshape(-1).cpu().numpy().astype(np.int32),
+                   self._offset.reshape(-1).cpu().numpy().astype(np.int32))
+            self._host_tables = hit
+        return hit[1:]
 
     # -- host range coder ----------------------------------------------------------------------
     def compress(self, inputs, indexes, means=None):
@@ -180,9 +183,14 @@ class EntropyBottleneck(EntropyModel):
 
     def _packed_params(self):
         key = tuple((p.data_ptr(), p._version) for p in list(self.matrices) + list(self.biases) + list(self.factors))
-        if self._packed is None or self._packed[0] != key:
-            self._packed = (key, eo.eb_pack_params(list(self.matrices), list(self.biases), list(self.factors)))
-        return self._packed[1]
+        hit = self._packed
+        if hit is None or hit[0] != key:
+            with so.pack_lock:                       # packed on the current stream: finished before any other stream sees it
+                hit = (key, eo.eb_pack_params(list(self.matrices), list(self.biases), list(self.factors)))
+                if hit[1].is_cuda:
+                    torch.cuda.current_stream().synchronize()
+                self._packed = hit
+        return hit[1]
 
     def update(self, force=False, update_quantiles=False):
         """Build the 16-bit CDF tables.  Always evaluated on the host in fp32, whatever device the parameters live on:

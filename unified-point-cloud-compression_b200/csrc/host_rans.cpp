@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <climits>
 #include <cstring>
+#include <cmath>
 #include <vector>
 
 namespace {
@@ -125,7 +126,7 @@ extern "C" int pcg_pmf_to_quantized_cdf(const float *pmf, int n, int precision, 
     uint64_t total = 0;
     for (int i = 0; i < n; ++i) {
         if (!(pmf[i] >= 0.f) || pmf[i] > 3.0e38f) return 1;
-        freq[i + 1] = (uint64_t)(pmf[i] * (float)(1 << precision) + 0.5f);
+        freq[i + 1] = (uint64_t)std::round(pmf[i] * (float)(1 << precision));     // compressai: std::round (fp32 product, half away from zero)
         total += freq[i + 1];
     }
     if (total == 0) return 2;

@@ -58,10 +58,13 @@ __global__ void k_table_clear(uint64_t *keys, int32_t *vals, long cap) {
     }
 }
 
-__global__ void k_hash_insert(const int32_t *__restrict__ coords, long n, uint64_t *keys, int32_t *vals, uint64_t mask) {
+// A coordinate outside the 16-bit-per-axis / 15-bit-batch packing range would wrap onto another voxel's key: it is not inserted
+// and bit 2 of *d_status is raised instead (the host side turns that into an error; MinkowskiEngine itself takes any int32).
+__global__ void k_hash_insert(const int32_t *__restrict__ coords, long n, uint64_t *keys, int32_t *vals, uint64_t mask, int32_t *d_status) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int4 c = pcg_ld_coord(coords, i);
+    if (!pcg_in_range(c.x, c.y, c.z, c.w)) { if (d_status) atomicOr(d_status, 2); return; }
     pcg_table_insert_min(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w), (int)i);
 }
 
@@ -93,12 +96,12 @@ extern "C" long pcg_nbr_pitch(long n_out) { return n_out <= 0 ? 128 : (n_out + 1
 
 extern "C" size_t pcg_scratch_bytes(long n_items) { return pcg_compact_scratch_bytes(n_items) + 8192; }
 
-extern "C" int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, void *stream) {
+extern "C" int pcg_hash_build(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap, int32_t *d_status, void *stream) {
     PCG_CHECK_ARG(is_pow2(cap) && cap >= n + 1, "pcg_hash_build: cap=%ld must be a power of two > n=%ld", cap, n);
     cudaStream_t st = as_stream(stream);
     if (int rc = clear_table(keys, vals, cap, st)) return rc;
     if (n > 0) {
-        k_hash_insert<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, keys, vals, (uint64_t)cap - 1);
+        k_hash_insert<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, keys, vals, (uint64_t)cap - 1, d_status);
         PCG_LAUNCHED();
     }
     return 0;
@@ -124,10 +127,11 @@ struct StridedKey {  // key of floor(c/step)*step for row i
     }
 };
 
-__global__ void k_insert_strided(StridedKey sk, long n, uint64_t *keys, int32_t *vals, uint64_t mask) {
+__global__ void k_insert_strided(StridedKey sk, long n, uint64_t *keys, int32_t *vals, uint64_t mask, int32_t *d_status) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int4 c = sk.coord(i);
+    if (!pcg_in_range(c.x, c.y, c.z, c.w)) { if (d_status) atomicOr(d_status, 2); return; }       // see k_hash_insert
     pcg_table_insert_min(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w), (int)i);
 }
 
@@ -138,6 +142,7 @@ struct FlagFirstStrided {
     uint64_t mask;
     __device__ bool operator()(long i) const {
         int4 c = sk.coord(i);
+        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
         return pcg_table_find(keys, vals, mask, pcg_pack(c.x, c.y, c.z, c.w)) == (int)i;
     }
 };
@@ -170,13 +175,14 @@ __global__ void k_remap_table(const int32_t *__restrict__ out_coords, const int3
 }
 
 static int unique_strided(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
-                          int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
+                          int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, int32_t *d_status, void *scratch,
                           size_t scratch_bytes, cudaStream_t st) {
     PCG_CHECK_ARG(is_pow2(cap) && cap >= n + 1, "unique/stride: cap=%ld must be a power of two > n=%ld", cap, n);
     PCG_CHECK_ARG(step >= 1, "unique/stride: step=%d", step);
     PcgScratch s;
     PCG_CHECK_ARG(pcg_carve_scratch(scratch, scratch_bytes, n, s), "unique/stride: scratch too small (%zu < %zu)",
                   scratch_bytes, pcg_compact_scratch_bytes(n));
+    if (d_status) PCG_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
     if (int rc = clear_table(keys, vals, cap, st)) return rc;
     if (n <= 0) {
         PCG_CUDA(cudaMemsetAsync(d_n_out, 0, sizeof(int32_t), st));
@@ -184,7 +190,7 @@ static int unique_strided(const int32_t *coords, long n, int step, uint64_t *key
     }
     StridedKey sk{coords, step};
     uint64_t mask = (uint64_t)cap - 1;
-    k_insert_strided<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(sk, n, keys, vals, mask);
+    k_insert_strided<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(sk, n, keys, vals, mask, d_status);
     PCG_LAUNCHED();
     if (int rc = pcg_compact(n, FlagFirstStrided{sk, keys, vals, mask}, EmitStrided{sk, out_coords, out_index}, d_n_out, s, st))
         return rc;
@@ -196,16 +202,16 @@ static int unique_strided(const int32_t *coords, long n, int step, uint64_t *key
 }
 
 extern "C" int pcg_unique_first(const int32_t *coords, long n, uint64_t *keys, int32_t *vals, long cap,
-                                int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, void *scratch,
+                                int32_t *out_coords, int32_t *out_index, int32_t *d_n_out, int32_t *d_status, void *scratch,
                                 size_t scratch_bytes, void *stream) {
-    return unique_strided(coords, n, 1, keys, vals, cap, out_coords, out_index, d_n_out, scratch, scratch_bytes,
+    return unique_strided(coords, n, 1, keys, vals, cap, out_coords, out_index, d_n_out, d_status, scratch, scratch_bytes,
                           as_stream(stream));
 }
 
 extern "C" int pcg_stride_coords(const int32_t *coords, long n, int step, uint64_t *keys, int32_t *vals, long cap,
-                                 int32_t *out_coords, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
+                                 int32_t *out_coords, int32_t *d_n_out, int32_t *d_status, void *scratch, size_t scratch_bytes,
                                  void *stream) {
-    return unique_strided(coords, n, step, keys, vals, cap, out_coords, nullptr, d_n_out, scratch, scratch_bytes,
+    return unique_strided(coords, n, step, keys, vals, cap, out_coords, nullptr, d_n_out, d_status, scratch, scratch_bytes,
                           as_stream(stream));
 }
 

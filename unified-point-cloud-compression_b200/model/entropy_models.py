@@ -103,6 +103,14 @@ class MeanScaleHyperprior(CompressionModel):
         self.rescale_nn = _mlp([2, 8, C // 4, C], nn.Softplus())
         self.quant_nn = _mlp([2, 10, 10, 1])
 
+    def prepare(self):
+        """Fill the lazily built caches of the entropy models (packed prior parameters, host CDF tables)."""
+        if self.entropy_bottleneck._quantized_cdf.numel():
+            self.entropy_bottleneck._tables()
+            self.gaussian_conditional._tables()
+        if next(self.entropy_bottleneck.parameters()).is_cuda:
+            self.entropy_bottleneck._packed_params()
+
     # -- pieces ------------------------------------------------------------------------------
     def get_offsets(self, stddev, scale):
         """Per-element MLP 2->10->10->1 on (scale, stddev) (entropy_models.py:218-233); torch path for training."""

@@ -46,6 +46,24 @@ class UnifiedModel(CompressionModel):
     def aux_loss(self):
         return self.entropy_model.aux_loss()
 
+    def prepare(self):
+        """Fill every lazily built cache of the inference path -- packed convolution weights, the fused heads' host copies,
+        the factorised prior's packed parameters, the host CDF tables -- and synchronise.  Call after the parameters are final
+        (load_state_dict / update()) and before frames are coded concurrently; codec.FramePipeline does it for its model."""
+        with torch.no_grad():
+            for m in self.modules():
+                if isinstance(m, ME.MinkowskiConvolutionBase):
+                    m.prepare()
+            for head in (self.g_s.predict_1, self.g_s.predict_2, self.g_s.predict_3):
+                first, last = head[0], head[2]
+                if first.kernel.is_cuda and so.head_fusable(first.kernel_size, first.kernel, last.kernel_size, last.kernel):
+                    first._packed.get(first.kernel.detach())
+                    so.head_host_params(first._packed, last.kernel, first.bias)
+            self.entropy_model.prepare()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        return self
+
     # -- training forward (model.py:45-90) -------------------------------------------------------
     def forward(self, x, q, Lambda):
         occ = torch.ones((x.C.shape[0], 1), device=x.device)

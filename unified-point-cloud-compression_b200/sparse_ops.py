@@ -5,6 +5,7 @@ do for the reference; all arithmetic happens in the CUD
 import contextlib
 import ctypes
 import os
+import threading
 import weakref
 
 import torch
@@ -43,6 +44,45 @@ def scratch(nbytes, device):
     return buf
 
 
+_ctl = {}
+
+RANGE_ERROR = ("coordinate outside the packing range of the GPU hash (batch in [0, 32767], x/y/z in [-32768, 32767]): "
+               "MinkowskiEngine accepts any int32, this graft does not (include/pcg.h, conventions)")
+
+
+def ctl(device):
+    """Per-(device, stream) int32 control words, zero-initialised once: [0] = sticky status of pcg_hash_build (the one table
+    builder without a size read-back of its own), [1:] = counters / status words of the call in flight.  Every C-ABI call
+    that takes a counter clears it itself, and every reader synchronises right after its call, so the words are reused."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    buf = _ctl.get(key)
+    if buf is None:
+        buf = _ctl[key] = torch.zeros(8, dtype=torch.int32, device=device)
+    return buf
+
+
+def read_ctl(c, n):
+    """Words [1, 1 + n) of a control buffer as python ints -- ONE blocking read-back, which also carries the sticky
+    coordinate-range status of every table built on this stream since the last read."""
+    vals = c[:1 + n].tolist()
+    if vals[0]:
+        c[0:1].zero_()
+        raise RuntimeError(RANGE_ERROR)
+    return vals[1:]
+
+
+def check_status(device):
+    """Raise if any table built on this stream since the last read-back met a coordinate outside the packing range."""
+    read_ctl(ctl(device), 0)
+
+
+# Packed-operand caches (weights, tables) are filled lazily and shared by every host thread / CUDA stream that runs the model
+# (codec.FramePipeline).  A miss is rare (first use, or a parameter changed): it is taken under this lock and the packing
+# stream is synchronised BEFORE the new buffer is published, so no other stream can consume a buffer that is still being
+# written; a hit takes no lock (one tuple read).  `UnifiedModel.prepare()` fills every cache up front.
+pack_lock = threading.RLock()
+
+
 def _need_cuda(t, what):
     if not t.is_cuda:
         raise RuntimeError(f"{what} must live on a CUDA device: the graft has no CPU path")
@@ -75,7 +115,7 @@ class CoordSet:
             keys = torch.empty(cap, dtype=torch.int64, device=dev)
             vals = torch.empty(cap, dtype=torch.int32, device=dev)
             with hbm_span("hash_build", (self.n,), 16.0 * self.n + 12.0 * cap):      # coordinates read, table (key + row) written
-                call("pcg_hash_build", ptr(self.coords), self.n, ptr(keys), ptr(vals), cap, stream())
+                call("pcg_hash_build", ptr(self.coords), self.n, ptr(keys), ptr(vals), cap, ptr(ctl(dev)[0:1]), stream())
             self._table = (keys, vals, cap)
         return self._table
 
@@ -101,13 +141,15 @@ class CoordSet:
             keys = torch.empty(cap, dtype=torch.int64, device=dev)
             vals = torch.empty(cap, dtype=torch.int32, device=dev)
             out = torch.empty((self.n, 4), dtype=torch.int32, device=dev)
-            cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+            c = ctl(dev)
             nb = _lib.load().pcg_scratch_bytes(max(self.n, 1))
             ws = scratch(nb, dev)
             with hbm_span("stride_coords", (self.n,), 16.0 * self.n + 12.0 * cap):      # lower bound: the 16 * n_out written rows not counted
-                call("pcg_stride_coords", ptr(self.coords), self.n, step, ptr(keys), ptr(vals), cap, ptr(out), ptr(cnt),
+                call("pcg_stride_coords", ptr(self.coords), self.n, step, ptr(keys), ptr(vals), cap, ptr(out), ptr(c[1:2]), ptr(c[2:3]),
                      ptr(ws), ws.numel(), stream())
-            n_out = int(cnt.item())
+            n_out, status = read_ctl(c, 2)
+            if status & 2:
+                raise RuntimeError(RANGE_ERROR)
             hit = CoordSet(out[:n_out], step, table=(keys, vals, cap))
             self._strided[stride] = hit
         return hit
@@ -130,14 +172,14 @@ class CoordSet:
                 keys = torch.empty(cap, dtype=torch.int64, device=dev)
                 vals = torch.empty(cap, dtype=torch.int32, device=dev)
                 out = torch.empty((max(max_out, 1), 4), dtype=torch.int32, device=dev)
-                cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+                c = ctl(dev)
                 ws = scratch(lib.pcg_scratch_bytes(max(n_cand, 1)), dev)
                 with hbm_span("generate_coords", (self.n, K), 16.0 * self.n + 12.0 * cap):   # lower bound, as above
                     call("pcg_generate_coords", ptr(self.coords), self.n, int(ksize), int(stride), ts_out, ptr(keys), ptr(vals), cap,
-                         ptr(out), max_out, ptr(cnt[0:1]), ptr(cnt[1:2]), ptr(ws), ws.numel(), stream())
-                n_out, status = (int(v) for v in cnt.tolist())
+                         ptr(out), max_out, ptr(c[1:2]), ptr(c[2:3]), ptr(ws), ws.numel(), stream())
+                n_out, status = read_ctl(c, 2)
                 if status & 2:
-                    raise RuntimeError("generated coordinate outside the 16-bit packing range")
+                    raise RuntimeError("generated " + RANGE_ERROR)
                 if status == 0:
                     break
                 if max_out >= n_cand:
@@ -160,14 +202,14 @@ class CoordSet:
             ckeys, cvals, ccap = cells.table()
             pitch = lib.pcg_nbr_pitch(cells.n)
             pnbr = torch.empty((27, pitch), dtype=torch.int32, device=dev)
-            cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+            c = ctl(dev)
             call("pcg_cells_parent_map", ptr(self.coords), self.n, self.ts, ptr(ckeys), ptr(cvals), ccap, cells.n, ptr(pnbr), pitch,
-                 ptr(cnt[1:2]), stream())
+                 ptr(c[2:3]), stream())
             mask = torch.empty(max(cells.n, 1), dtype=torch.uint8, device=dev)
             base = torch.empty(max(cells.n, 1), dtype=torch.int32, device=dev)
             ws = scratch(lib.pcg_cells_scratch_bytes(max(cells.n, 1)), dev)
-            call("pcg_cells_info", ptr(pnbr), pnbr.shape[1], cells.n, ptr(mask), ptr(base), ptr(cnt[0:1]), ptr(ws), ws.numel(), stream())
-            n_out, status = (int(v) for v in cnt.tolist())
+            call("pcg_cells_info", ptr(pnbr), pnbr.shape[1], cells.n, ptr(mask), ptr(base), ptr(c[1:2]), ptr(ws), ws.numel(), stream())
+            n_out, status = read_ctl(c, 2)
             if status:
                 raise RuntimeError("pcg_cells_parent_map: a dilated parent position is missing from the cell table")
             out = torch.empty((n_out, 4), dtype=torch.int32, device=dev)
@@ -269,11 +311,13 @@ def unique_first(coords):
     vals = torch.empty(cap, dtype=torch.int32, device=dev)
     out = torch.empty((max(n, 1), 4), dtype=torch.int32, device=dev)
     index = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
-    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    c = ctl(dev)
     ws = scratch(lib.pcg_scratch_bytes(max(n, 1)), dev)
-    call("pcg_unique_first", ptr(coords), n, ptr(keys), ptr(vals), cap, ptr(out), ptr(index), ptr(cnt), ptr(ws),
+    call("pcg_unique_first", ptr(coords), n, ptr(keys), ptr(vals), cap, ptr(out), ptr(index), ptr(c[1:2]), ptr(c[2:3]), ptr(ws),
          ws.numel(), stream())
-    m = int(cnt.item())
+    m, status = read_ctl(c, 2)
+    if status & 2:
+        raise RuntimeError(RANGE_ERROR)
     return out[:m], index[:m], (keys, vals, cap)
 
 
@@ -337,11 +381,18 @@ class PackedWeights:
     kind "umma": K-major swizzled tiles for tcgen05; kind "mma": mma.sync B fragments for the narrow-head kernel."""
 
     def __init__(self):
-        self.key, self.buf = None, None
+        self.entry = None                  # (key, buffer), published as ONE object
+        self._proj_host = None
 
     def get(self, w3, kind="umma"):
         key = (w3.data_ptr(), w3._version, tuple(w3.shape), kind)
-        if key != self.key:
+        hit = self.entry
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        with pack_lock:
+            hit = self.entry
+            if hit is not None and hit[0] == key:
+                return hit[1]
             K, cin, cout = w3.shape
             lib = _lib.load()
             if kind == "im2col":        # (K,cin,cout) seen as one dense (1, roundup64(K*cin), cout) kernel
@@ -353,8 +404,9 @@ class PackedWeights:
             buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
             call("pcg_pack_weights_bf16" if kind == "umma" else "pcg_pack_weights_mma", ptr(w3.contiguous()), K, cin, cout,
                  ptr(buf), stream())
-            self.key, self.buf = key, buf
-        return self.buf
+            torch.cuda.current_stream().synchronize()
+            self.entry = (key, buf)
+        return buf
 
 
 class ConvProfiler:
@@ -418,6 +470,22 @@ def tc_eligible(K, cin, cout):
     return K <= 128 and cout <= 256 and K * cin >= 32 and not (K == 1 and cout < 16)
 
 
+def narrow_rule(K, cin, cout):
+    """Static rule: layers that take the register-gather mma.sync kernel (k_conv_mma) in "auto" mode."""
+    return _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
+        (cin <= 16 or os.environ.get("PCG_NARROW") == "mma") and os.environ.get("PCG_NARROW") != "tc" and \
+        _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+
+
+def pack_kind(K, cin, cout, fp32_input=True):
+    """Operand image the static rules of sparse_conv pick for a (K,cin,cout) kernel in the current mode; None = fp32 SIMT path."""
+    if _conv_mode == "f32" or not tc_eligible(K, cin, cout):
+        return None
+    if _conv_mode == "auto" and fp32_input and im2col_eligible(K, cin, cout):
+        return "im2col"
+    return "mma" if narrow_rule(K, cin, cout) else "umma"
+
+
 def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT_NONE, packed=None, out="f32"):
     """out[o] = act(bias + sum_i F[nbr[i][o]] @ W[i]).
 
@@ -456,8 +524,7 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     # (the LSU-gather tcgen05 kernel handles 32 / 64-byte rows too and is faster on the 32->16 and 64->1 heads -- level-3 candidates:
     # 1.20 against 1.47 ms, level 2: 0.46 against 0.60 -- while the 16->1 layer stays on k_conv_mma, 0.68 against 0.76 ms;
     # static shape rule, PCG_NARROW=mma sends every head layer to k_conv_mma for A/B runs)
-    narrow = use_tc and _conv_mode == "auto" and cin <= 64 and cout <= 16 and K <= 128 and \
-        (cin <= 16 or os.environ.get("PCG_NARROW") == "mma") and os.environ.get("PCG_NARROW") != "tc" and _lib.load().pcg_mma_weight_bytes(K, cin, cout) <= 160 * 1024
+    narrow = use_tc and narrow_rule(K, cin, cout)
     is_head = cin <= 64 and cout <= 16          # gather-bound occupancy-head layers: reported with the HBM/L2-bound kernels
     if use_tc and _conv_mode == "auto" and feats.dtype == torch.float32 and im2col_eligible(K, cin, cout):
         rows = im2col_row_elems(K, cin)
@@ -549,6 +616,20 @@ def head_fusable(ksize_a, w_a, ksize_b, w_b):
             and tc_eligible(K, cin, cmid) and not im2col_eligible(K, cin, cmid))
 
 
+def head_host_params(packed, w_b, b_a):
+    """Host copies of the fused head's second-layer kernel (27, cmid) and first-layer bias: they travel in the launch's kernel
+    parameters (constant bank).  Made once per parameter version and cached on the first layer's PackedWeights."""
+    key = (w_b.data_ptr(), w_b._version, None if b_a is None else (b_a.data_ptr(), b_a._version))
+    hit = getattr(packed, "_proj_host", None) if packed is not None else None
+    if hit is None or hit[0] != key:
+        with pack_lock:                    # .cpu() synchronises; the tuple is published as one object
+            hit = (key, w_b.detach().reshape(27, -1).float().cpu().contiguous(),
+                   None if b_a is None else b_a.detach().reshape(-1).float().cpu().contiguous())
+            if packed is not None:
+                packed._proj_host = hit
+    return hit[1], hit[2]
+
+
 def occupancy_head(feats, cset, w_a, b_a, w_b, b_b, packed=None):
     """logit = conv_b(relu(conv_a(x))) on one coordinate set (model/transforms.py:146-160), second layer GEMM-first:
     the first layer's epilogue (tcgen05 kernel, thread = output row, fp32 accumulator row in registers) also forms the 27 dot
@@ -567,16 +648,7 @@ def occupancy_head(feats, cset, w_a, b_a, w_b, b_b, packed=None):
     fb = to_bf16(feats)
     wp = (packed or PackedWeights()).get(w_a.detach())
     bb = b_b.reshape(-1).contiguous() if b_b is not None else None
-    # the second layer's kernel and the first layer's bias travel in the launch's kernel parameters (constant bank): host copies,
-    # made once per parameter version
-    key = (w_b.data_ptr(), w_b._version, None if b_a is None else (b_a.data_ptr(), b_a._version))
-    hit = getattr(packed, "_proj_host", None) if packed is not None else None
-    if hit is None or hit[0] != key:
-        hit = (key, w_b.detach().reshape(27, cmid).float().cpu().contiguous(),
-               None if b_a is None else b_a.detach().reshape(-1).float().cpu().contiguous())
-        if packed is not None:
-            packed._proj_host = hit
-    w2, ba_host = hit[1], hit[2]
+    w2, ba_host = head_host_params(packed, w_b, b_a)
     planes = torch.empty((27, pitch), dtype=torch.float32, device=dev)
     prof = profiler
     if prof is not None:
@@ -602,11 +674,17 @@ class PackedGemmWeights:
     """bf16 operand image of a (K,cin,cout) kernel seen as the dense matrix [cin x K*cout] in column groups of 256."""
 
     def __init__(self):
-        self.key, self.buf = None, None
+        self.entry = None
 
     def get(self, w3):
         key = (w3.data_ptr(), w3._version, tuple(w3.shape))
-        if key != self.key:
+        hit = self.entry
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        with pack_lock:
+            hit = self.entry
+            if hit is not None and hit[0] == key:
+                return hit[1]
             K, cin, cout = w3.shape
             n_cols = K * cout
             G = (n_cols + 255) // 256
@@ -616,8 +694,9 @@ class PackedGemmWeights:
             nbytes = _lib.load().pcg_packed_weight_bytes(G, cin, 256)
             buf = torch.empty(nbytes, dtype=torch.uint8, device=w3.device)
             call("pcg_pack_weights_bf16", ptr(wg), G, cin, 256, ptr(buf), stream())
-            self.key, self.buf = key, buf
-        return self.buf
+            torch.cuda.current_stream().synchronize()
+            self.entry = (key, buf)
+        return buf
 
 
 def cells_eligible(ksize, stride, cin, cout):
@@ -716,7 +795,7 @@ def prune_rows(coords, feats, mask, n_keep=None):
     m8 = (mask.view(torch.uint8) if mask.dtype == torch.bool else mask.to(torch.uint8)).contiguous()
     lib = _lib.load()
     ws = scratch(lib.pcg_scratch_bytes(max(n, 1)) + 4 * max(n, 1), dev)
-    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    cnt = ctl(dev)[3:4]                    # written by the compaction itself (never read back here)
     # size unknown: count first (one sync), then compact into exact buffers
     bound = int(m8.sum().item()) if n_keep is None else int(n_keep)
     oc = torch.empty((bound, 4), dtype=torch.int32, device=dev) if coords is not None else None
@@ -748,7 +827,7 @@ def prune_rows_reordered(coords, feats, mask, n_keep):
     lib = _lib.load()
     n_keep = int(n_keep)
     rows = torch.empty(max(n_keep, 1), dtype=torch.int32, device=dev)
-    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    cnt = ctl(dev)[3:4]
     ws = scratch(lib.pcg_scratch_bytes(max(n, 1)), dev)
     call("pcg_mask_to_rows", ptr(m8.contiguous()), n, ptr(rows), ptr(cnt), ptr(ws), ws.numel(), stream())
     rows = rows[:n_keep]
