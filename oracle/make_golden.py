@@ -73,9 +73,56 @@ def make(name, cfg_name, seed, q):
     print(name, "points", len(pts), "k", ks, "bytes y/z", len(bits[0][0][0]), len(bits[0][1][0]), "rec", tuple(rec.shape))
 
 
+def make_losses(name="ref_losses", seed=3, q=(0.4, 0.8), lam=(0.7, 1.3)):
+    """Loss values of the reference's UNMODIFIED loss.py (/root/reference/loss.py:9-274: Loss, BPPLoss, ColorLoss,
+    Multiscale_FocalLoss, ShepardsLoss with utils.overlapping_mask) on the training forward of its own model, both for the
+    `loss:` section of configs/CVPR_inverse_scaling.yaml and of configs/CVPR_inverse_scaling_shepard.yaml.  The fixture keeps
+    the complete forward output (prediction, the three occupancy predictions, the three ground-truth coordinate sets, both
+    likelihood tensors), so the product's loss mirror can be checked on IDENTICAL inputs, and the weights + input so the whole
+    chain (product forward -> product loss) can be checked too."""
+    import copy
+    cfg = small_config("CVPR_inverse_scaling")
+    net = shim.reference_model(cfg, seed=seed)
+    spread_weights(net)
+    import MinkowskiEngine as ME
+    import loss as ref_loss        # the reference's file (imports its utils.py over the open3d stand-in)
+    clouds = [synth.small_cloud(seed=seed + 1 + b, radius=9.0 + b, centre=(18, 18, 18), n_samples=6000) for b in range(2)]
+    coords = torch.cat([torch.cat([torch.full((len(p), 1), b, dtype=torch.int32), torch.from_numpy(p).int()], 1) for b, (p, _) in enumerate(clouds)])
+    feats = torch.cat([torch.from_numpy(c.astype(np.float32)) for _, c in clouds])
+    qt = torch.tensor([q, q[::-1]], dtype=torch.float32)
+    lam_t = torch.tensor([lam, (1.1, 0.6)], dtype=torch.float32)
+    store = {}
+    with torch.no_grad():
+        x = ME.SparseTensor(coordinates=coords, features=feats)
+        out = net(x, qt, lam_t)
+        for cfg_name in ("CVPR_inverse_scaling", "CVPR_inverse_scaling_shepard"):
+            loss_cfg = yaml.safe_load(open(os.path.join(shim.REFERENCE, "configs", cfg_name + ".yaml")))["loss"]
+            pred = dict(out, occ_predictions=list(out["occ_predictions"]), points=list(out["points"]))   # (the focal loss reverses the lists in place)
+            total, parts = ref_loss.Loss(copy.deepcopy(loss_cfg))(x, pred)
+            tag = "shepard" if cfg_name.endswith("shepard") else "default"
+            store[f"loss/{tag}/total"] = np.float64(total)
+            for k, v in parts.items():
+                store[f"loss/{tag}/{k}"] = np.float64(v)
+            print(name, tag, float(total), {k: float(v) for k, v in parts.items()})
+    for i in range(3):
+        store[f"occ{i}_C"], store[f"occ{i}_F"] = out["occ_predictions"][i].C.numpy(), out["occ_predictions"][i].F.numpy()
+        store[f"points{i}_C"] = out["points"][i].C.numpy()
+        store[f"points{i}_ts"] = np.asarray(out["points"][i].tensor_stride[0])
+        store[f"occ{i}_ts"] = np.asarray(out["occ_predictions"][i].tensor_stride[0])
+    np.savez_compressed(
+        os.path.join(OUT, name + ".npz"), cfg_name="CVPR_inverse_scaling", width=8, q=qt.numpy(), lam=lam_t.numpy(),
+        coords=coords.numpy(), colors=feats.numpy(), pred_C=out["prediction"].C.numpy(), pred_F=out["prediction"].F.numpy(),
+        lik_y=out["likelihoods"]["y"].numpy(), lik_z=out["likelihoods"]["z"].numpy(),
+        **store, **{"sd/" + k: v.numpy() for k, v in net.state_dict().items()})
+
+
 if __name__ == "__main__":
     assert shim.available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
-    make("ref_inverse_scaling", "CVPR_inverse_scaling", 0, (0.5, 0.5))
-    make("ref_inverse_nn", "CVPR_inverse_nn", 1, (0.2, 0.9))
-    make("ref_fixed_R1", "CVPR_inverse_scaling_fixed_R1", 2, (0.0, 0.0))
+    what = sys.argv[1:] or ["codec", "losses"]
+    if "codec" in what:
+        make("ref_inverse_scaling", "CVPR_inverse_scaling", 0, (0.5, 0.5))
+        make("ref_inverse_nn", "CVPR_inverse_nn", 1, (0.2, 0.9))
+        make("ref_fixed_R1", "CVPR_inverse_scaling_fixed_R1", 2, (0.0, 0.0))
+    if "losses" in what:
+        make_losses()

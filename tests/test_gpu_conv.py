@@ -1,5 +1,7 @@
 """CUDA sparse convolution (fp32 SIMT and tcgen05 bf16) vs the fp32 oracle, on identical inputs.
 Tolerances (north-star): fp32 path 1e-5 relative L2; bf16 tensor-core path 1e-2 relative L2."""
+import importlib
+
 import numpy as np
 import pytest
 import torch
@@ -321,3 +323,51 @@ def test_conv_gradients_match_oracle_autograd(pkg, dev, cin, cout, ksize, stride
     for name, got, want in (("d_input", Fd.grad, Fr.grad), ("d_weight", Wd.grad, Wr.grad), ("d_bias", bd.grad, br.grad)):
         err = rel_l2(got.cpu().numpy(), want.numpy())
         assert err < 5e-5, f"{name}: rel-L2 {err:.3e}"
+
+
+@pytest.mark.parametrize("cin,cout,ksize,stride", [(128, 128, 5, 2), (192, 192, 2, 2), (24, 40, 3, 2), (16, 8, 3, 1)])
+def test_conv_transpose_onto_given_coordinates_matches_oracle(pkg, dev, cin, cout, ksize, stride):
+    """ME4: `MinkowskiConvolutionTranspose` (non-generative) -- the transposed convolution onto a coordinate set the CALLER gives
+    (a SparseTensor or a bare (N,4) tensor), here a random half of the generative children plus voxels no parent reaches
+    (their rows are bias only).  Same arithmetic as ME3 on another output set (no call site in the reference)."""
+    ME = importlib.import_module(pkg.__name__ + ".MinkowskiEngine")
+    so = pkg.sparse_ops
+    ts_in = 2 * stride
+    C, cs = setup(dev, pkg, seed=cin + ksize, ts=ts_in)
+    ts_out = ts_in // stride
+    rng = np.random.default_rng(cin + cout)
+    children = me_ref.generate_coords(C, ts_out, ksize)
+    keep = children[rng.random(len(children)) < 0.5]
+    far = np.array([[0, 400, 400, 400], [0, 402 * ts_out, 0, 0]], np.int32) * np.array([1, ts_out, ts_out, ts_out], np.int32)
+    C_out = np.concatenate([keep, far]).astype(np.int32)
+    K = ksize ** 3
+    Fm = rng.standard_normal((len(C), cin)).astype(np.float32)
+    W = (rng.standard_normal((K, cin, cout)) / np.sqrt(cin * K) * 3).astype(np.float32)
+    b = rng.standard_normal((1, cout)).astype(np.float32)
+    ref = oracle_conv(C, C_out, Fm, W, b, ksize, ts_out, True)
+    assert np.allclose(ref[-2:], b)                                     # unreachable voxels: bias only
+    conv = ME.MinkowskiConvolutionTranspose(in_channels=cin, out_channels=cout, kernel_size=ksize, stride=stride, bias=True, dimension=3).to(dev)
+    with torch.no_grad():
+        conv.kernel.copy_(torch.from_numpy(W))
+        conv.bias.copy_(torch.from_numpy(b))
+        x = ME.SparseTensor(torch.from_numpy(Fm).to(dev), _coord_set=cs)
+        target = ME.SparseTensor(features=torch.zeros((len(C_out), 1), device=dev), coordinates=torch.from_numpy(C_out).to(dev),
+                                 tensor_stride=ts_out, device=dev)
+        modes = [("f32", 2e-5)] + ([("auto", 1e-2)] if so.tc_eligible(K, cin, cout) else [])
+        for mode, tol in modes:
+            prev = so.set_conv_mode(mode)
+            try:
+                out_a = conv(x, target)                                  # coordinates as a SparseTensor
+                out_b = conv(x, torch.from_numpy(C_out).to(dev))         # coordinates as an (N,4) tensor
+            finally:
+                so.set_conv_mode(prev)
+            for out in (out_a, out_b):
+                assert out.tensor_stride == [ts_out] * 3 and np.array_equal(out.C.cpu().numpy(), C_out)
+                err = rel_l2(out.F.cpu().numpy(), ref)
+                assert err < tol, f"{mode}: rel-L2 {err:.3e}"
+        with pytest.raises(ValueError):
+            conv(x)                                                      # the output set is not optional
+        wrong = ME.SparseTensor(features=torch.zeros((len(C_out), 1), device=dev), coordinates=torch.from_numpy(C_out).to(dev),
+                                tensor_stride=ts_in, device=dev)
+        with pytest.raises(RuntimeError):
+            conv(x, wrong)                                               # wrong tensor stride

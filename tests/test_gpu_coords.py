@@ -1,4 +1,6 @@
 """CUDA coordinate kernels vs the oracle: bit-exact rows, order included (first-occurrence order == ME CPU)."""
+import importlib
+
 import numpy as np
 import pytest
 import torch
@@ -290,3 +292,28 @@ def test_compaction_keeps_input_order_at_every_tile_boundary(pkg, dev, n, densit
     want = torch.nonzero(mask).reshape(-1)
     assert oc.shape[0] == want.shape[0]
     assert torch.equal(of.reshape(-1).long(), want) and torch.equal(oc, coords[want])
+
+
+def test_out_of_range_coordinates_raise_instead_of_wrapping(pkg, dev):
+    """The hash packs (b, x, y, z) into 15 + 3 x 16 bits; a coordinate outside that range must raise (MinkowskiEngine takes any
+    int32 -- here it would wrap onto another voxel's key and merge two voxels silently): ctor / unique_first, strided sets,
+    and a table built lazily from caller-given rows (sticky status, read at the next size read-back)."""
+    so = pkg.sparse_ops
+    ME = importlib.import_module(pkg.__name__ + ".MinkowskiEngine")
+    good = torch.tensor([[0, 1, 2, 3], [0, 4, 5, 6], [0, 32767, -32768, 0]], dtype=torch.int32, device=dev)
+    t = ME.SparseTensor(features=torch.ones((3, 1), device=dev), coordinates=good, device=dev)
+    assert t.C.shape[0] == 3
+    for bad_row in ([0, 32768, 0, 0], [0, 0, -32769, 0], [32768, 0, 0, 0], [0, 1, 2, 3 + 65536]):
+        bad = torch.cat([good, torch.tensor([bad_row], dtype=torch.int32, device=dev)])
+        with pytest.raises(RuntimeError, match="packing range"):
+            ME.SparseTensor(features=torch.ones((4, 1), device=dev), coordinates=bad, device=dev)
+        with pytest.raises(RuntimeError, match="packing range"):
+            so.unique_first(bad)
+        cs = so.CoordSet(bad, 1)                     # trusted construction: no check yet
+        with pytest.raises(RuntimeError, match="packing range"):
+            cs.strided(2)
+        cs = so.CoordSet(bad, 1)
+        cs.table()                                   # lazily built table: the status is sticky ...
+        with pytest.raises(RuntimeError, match="packing range"):
+            so.check_status(dev)                     # ... and surfaces at the next read-back
+        so.check_status(dev)                         # cleared after it was reported
