@@ -32,9 +32,11 @@ def test_compress_decompress_against_reference_golden(pkg, dev, name, mode):
         pkg.sparse_ops.set_conv_mode(prev)
 
 
-def _golden_roundtrip(pkg, dev, name, strict):
+def _golden_roundtrip(pkg, dev, name, strict, make_net=None):
+    """make_net(config, state_dict, device): model factory; default = the product's host mirror (tests/test_gpu_dropin.py passes
+    the reference's own UnifiedModel class imported over the drop-in packages)."""
     z, sd = load_golden(name)
-    net = build_product_model(pkg, golden_config(z), sd, dev)
+    net = (make_net or (lambda c, s, d: build_product_model(pkg, c, s, d)))(golden_config(z), sd, dev)
     q = torch.from_numpy(z["q"]).reshape(1, 2).to(dev)
     pc = torch.from_numpy(np.concatenate([z["points"].astype(np.float32), z["colors"]], axis=1)).to(dev)
     with torch.no_grad():
@@ -102,6 +104,17 @@ def test_eval_forward_against_reference_golden(pkg, dev, mode):
 def test_codec_roundtrip_vs_oracle_pipeline(pkg, dev, width, mode):
     stats = tiny_codec_roundtrip(pkg, dev, width=width, mode=mode)
     print(f"width={width} mode={mode}: {stats}")
+
+
+@pytest.mark.parametrize("mode", ["f32", "auto"])
+def test_block128_width128_vs_oracle_pipeline(pkg, dev, mode):
+    """BASELINE configs[0] at full size: the 128^3 block (oracle/synth.py::block128, 22 242 voxels) through the codec at the
+    configured widths (128 channels, 192 hyper channels) against oracle/pipeline_ref.py -- multi-wave grids, the two-tiles-per-CTA
+    kernels and > 1-tile compactions as the static rules select them, not forced by knobs."""
+    from oracle import synth
+    stats = tiny_codec_roundtrip(pkg, dev, width=128, mode=mode, cloud=synth.block128(seed=0))
+    print(f"block128 width=128 mode={mode}: {stats}")
+    assert stats["n"] == 22242
 
 
 def test_encoder_decoder_agree_on_indexes_bitwise(pkg, dev):
