@@ -32,11 +32,15 @@ UNIT = "Mpoints/s"
 
 
 def peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written per pool) or the profiling recipe's fallback.
+    bf16_burst: cuBLAS timed alone at full clocks -- the denominator for kernels timed one by one with CUDA events (the roofline
+    pass below) when the clock record shows no power cap; bf16_sustained: the same GEMM back to back under the 1 kW cap."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
-    return {"hbm_gbs": 6650.0, "bf16_tflops": 1400.0, "src": "fallback"}
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_burst": d["bf16_tflops"], "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "src": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "src": "fallback"}
 
 
 def model_config():
@@ -54,11 +58,9 @@ def make_frame(workload, seed):
 
 
 def cpu_sample(pts, rgb, workload):
-    """Bounded sample of the workload for the CPU arm: the cap of the top sphere (same surface statistics)."""
-    if workload != "frame10":
-        return pts, rgb, "whole 128^3 block"
-    sel = pts[:, 1] >= 700
-    return pts[sel], rgb[sel], f"crop y>=700 of the 10-bit frame ({int(sel.sum())} voxels: the two upper spheres)"
+    """The CPU arm codes the SAME unit as the GPU arm (one whole frame / block per step; ~7 s for the 10-bit frame on 16 cores)."""
+    return pts, rgb, {"frame10": "the whole 10-bit frame", "frame11": "the whole 11-bit frame", "block128": "the whole 128^3 block"}[workload] + \
+        f" ({len(pts)} voxels), encode + decode, one frame per step"
 
 
 # ----------------------------------------------------------------------------------------- clocks
@@ -169,12 +171,15 @@ def main():
         if rank != 0:
             return
         w = max(1, min(args.warmup, 1))
-        r = run_cpu(args.workload, max(1, args.steps), w)
+        r = run_cpu(args.workload, max(1, min(args.steps, 5)), w)     # a 10-bit frame is ~7 s of CPU work: at most 5 timed steps
         line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": w, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": config,
                 "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        line["steps"] = max(1, min(args.steps, 5))
+        line["config"]["workload"] = f"CVPR_inverse_scaling {args.workload}: 1 synthetic surface-sampled frame per step, compress+decompress, " \
+                                     "random-init weights, q=(0.5,0.5) (CPU arm: one frame at a time on all host cores)"
         emit(line)
         return
 
@@ -339,6 +344,10 @@ def main():
     tc_ms, tc_flops, tc_launches = (sum(t[k] for t in tcs) for k in ("ms", "flops", "launches"))
     all_conv_ms = sum(v["ms"] for k, v in prof.items() if k in ("conv_tc", "gemm_first", "gent_reduce", "conv_narrow", "conv_f32", "head_gather"))
     achieved = tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    # the roofline pass times kernels one by one: burst peak unless the clock record of the timed region shows the power cap
+    capped = bool(clk and "sw_power_cap" in (clk.get("reasons") or []))
+    peak_kind = "bf16_tflops_sustained (sw_power_cap seen)" if capped else "bf16_tflops (burst: kernels timed one by one, no power cap seen)"
+    bf16_peak = pk["bf16_sustained"] if capped else pk["bf16_burst"]
 
     def shapes(kind):
         d = prof.get(kind, zero)["by_shape"]
@@ -357,7 +366,8 @@ def main():
     if os.path.exists(tp) and args.workload == "frame10":
         traffic = json.load(open(tp))["tcgen05_conv_dram_bytes_per_step"]
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_mt / k_conv_tc + k_gemm_first (tcgen05 sparse conv kernels, all launches of one step)",
-                "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops"],
+                "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s", "frac": achieved / bf16_peak,
+                "peak_kind": peak_kind, "frac_of_burst_peak": achieved / pk["bf16_burst"], "frac_of_sustained_peak": achieved / pk["bf16_sustained"],
                 "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu --set full; source named in profiles/r01_traffic.json)",
                 "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
                 "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * depth / ms_res if ms_res else None,

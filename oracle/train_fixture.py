@@ -1,0 +1,92 @@
+"""Train a small codec with the reference's OWN training step and write its weights as a test fixture.
+TEST INFRASTRUCTURE; build container only (needs /root/reference):
+
+    python -m oracle.train_fixture [steps]        ->  tests/golden/trained_w32.npz
+
+Why: with random-init weights the occupancy logits are barely separated, so bf16 tensor-core rounding legitimately flips top-k
+membership and the end-to-end parity gates of the timed (bf16) mode can only be loose.  A TRAINED model separates occupied from
+empty candidates by many logits, which is the regime the codec is deployed in: on these weights the bf16 path must reproduce the
+fp32 oracle's decode almost voxel for voxel (tests/test_gpu_model.py::test_trained_codec_*).
+
+What runs: the reference's unmodified model/model.py (UnifiedModel.forward, train mode with its noise quantisation), loss.py
+(focal + colour + bpp-y + bpp-z, configs/CVPR_inverse_scaling.yaml `loss:`), data/q_func.py (random q per step, quadratic lambda
+map with the yaml's ranges) and the step of train.py:195-234 (two Adam optimisers, clip 1.0, aux loss) -- on top of the CPU oracle
+(oracle/shim.py, torch autograd).  Widths 32 (hyper 32); data: synthetic surface clouds (oracle/synth.py), two per step.
+Learning rate 2e-3 instead of the yaml's 1e-4: a few hundred steps, not 300 epochs.
+"""
+import os
+import random
+import sys
+import time
+
+import numpy as np
+import torch
+import yaml
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import shim, synth  # noqa: E402
+from oracle.make_golden import small_config  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden", "trained_w32.npz")
+
+
+def batch(step, n_clouds=2):
+    rng = np.random.default_rng(1000 + step)
+    coords, feats = [], []
+    for b in range(n_clouds):
+        r = float(rng.uniform(8.0, 13.0))
+        c = tuple(int(v) for v in rng.integers(18, 30, 3))
+        pts, rgb = synth.small_cloud(seed=int(rng.integers(1 << 30)), radius=r, centre=c, n_samples=int(700 * r * r / 10))
+        coords.append(torch.cat([torch.full((len(pts), 1), b, dtype=torch.int32), torch.from_numpy(pts).int()], 1))
+        feats.append(torch.from_numpy(rgb.astype(np.float32)))
+    return torch.cat(coords), torch.cat(feats)
+
+
+def main(steps=400, width=32, lr=2e-3):
+    assert shim.available(), "needs /root/reference"
+    cfg_all = yaml.safe_load(open(os.path.join(shim.REFERENCE, "configs", "CVPR_inverse_scaling.yaml")))
+    cfg = small_config("CVPR_inverse_scaling", width=width)
+    net = shim.reference_model(cfg, seed=0)
+    import MinkowskiEngine as ME          # the oracle, through the shim
+    import loss as ref_loss               # /root/reference/loss.py
+    from data.q_func import Q_Func        # /root/reference/data/q_func.py
+    random.seed(0)
+    torch.manual_seed(0)
+    net.train()
+    model_params = [p for n, p in net.named_parameters() if not n.endswith(".quantiles")]
+    bottleneck_params = [p for n, p in net.named_parameters() if n.endswith(".quantiles")]
+    opt = torch.optim.Adam(model_params, lr=lr)
+    opt_b = torch.optim.Adam(bottleneck_params, lr=cfg_all["bottleneck_learning_rate"])
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=max(steps * 2 // 3, 1), gamma=0.2)
+    loss_fn = ref_loss.Loss(cfg_all["loss"])
+    q_func = Q_Func(cfg_all["q_map"])
+    t0 = time.time()
+    for step in range(steps):
+        opt.zero_grad()
+        opt_b.zero_grad()
+        coords, feats = batch(step)
+        coords, feats = ME.utils.sparse_quantize(coordinates=coords, features=feats, quantization_size=1.0)
+        x = ME.SparseTensor(features=feats, coordinates=coords)
+        q, lam = q_func(x)
+        out = net(x, q, lam)
+        loss, parts = loss_fn(x, out)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(net.parameters(), cfg_all["clip_grad_norm"])
+        opt.step()
+        aux = net.aux_loss()
+        aux.backward()
+        opt_b.step()
+        sched.step()
+        if step % 20 == 0 or step == steps - 1:
+            print(f"step {step:4d} loss {float(loss):10.3f} " + " ".join(f"{k}={float(v):.4f}" for k, v in parts.items()) +
+                  f" aux {float(aux):.2f} q=({float(q[0, 0]):.2f},{float(q[0, 1]):.2f}) {time.time() - t0:.0f}s", flush=True)
+    net.eval()
+    net.update()
+    sd = {k: v.detach().numpy() for k, v in net.state_dict().items()}
+    np.savez_compressed(OUT, cfg_name="CVPR_inverse_scaling", width=width, steps=steps, **{"sd/" + k: v for k, v in sd.items()})
+    print("wrote", OUT, os.path.getsize(OUT), "bytes")
+
+
+if __name__ == "__main__":
+    main(int(sys.argv[1]) if len(sys.argv) > 1 else 400)
