@@ -100,6 +100,11 @@ int pcg_kernel_map(const uint64_t *keys, const int32_t *vals, long cap, const in
  * per block at the codec's entry so that every derived row order is spatially coherent. */
 int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t *perm, void *scratch, size_t scratch_bytes,
                   void *stream);
+/* The same stable sort restricted to key bits [begin_bit, end_bit) (keys: morton = 0: b:16|x:16|y:16|z:16, coordinates biased by
+ * 32768; morton = 1: b:16 | 48 interleaved bits).  morton = 1 with bits [0, 36) orders by the low 12 bits of every axis: a
+ * locality-only Z-order (row order is free in MinkowskiEngine semantics) in 5 radix passes instead of 8. */
+int pcg_sort_rows_bits(const int32_t *coords, long n, int morton, int begin_bit, int end_bit, int32_t *perm, void *scratch,
+                       size_t scratch_bytes, void *stream);
 size_t pcg_sort_rows_scratch_bytes(long n);
 
 /* Block entry (model/model.py:142-161): (n,6) float rows [x y z r g b] -> coords[i] = (batch, floor(xyz[perm[i]])),
@@ -240,6 +245,10 @@ int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_
 /* out_coords[r] = coords[rows[r]], out_feats[r] = feats[rows[r]] (c fp32 channels) for r < n_rows; either pair may be NULL. */
 int pcg_gather_rows(const int32_t *coords, const float *feats, int c, const int32_t *rows, long n_rows, int32_t *out_coords,
                     float *out_feats, void *stream);
+/* The same gather from bf16 source rows (c % 8 == 0) into fp32 output rows: survivors of a prune whose candidate rows exist
+ * only as the bf16 operand image the up-sampling kernel emitted (no fp32 copy of the ~20x larger candidate set is ever written). */
+int pcg_gather_rows_bf16(const int32_t *coords, const void *feats_bf16, int c, const int32_t *rows, long n_rows,
+                         int32_t *out_coords, float *out_feats, void *stream);
 
 /* ---- interpolation: SparseTensor.features_at_coordinates (ME6) ---------------------------------
  * Trilinear over the 2^3 corners at spacing ts; absent corners contribute 0.  query: nq x 4 fp32. */

@@ -317,3 +317,33 @@ def test_out_of_range_coordinates_raise_instead_of_wrapping(pkg, dev):
         with pytest.raises(RuntimeError, match="packing range"):
             so.check_status(dev)                     # ... and surfaces at the next read-back
         so.check_status(dev)                         # cleared after it was reported
+
+
+@pytest.mark.parametrize("c", [32, 128])
+def test_gather_rows_from_bf16_rows(pkg, dev, c):
+    """pcg_gather_rows_bf16: survivors of a prune gathered from bf16 candidate rows come back as the exact fp32 images."""
+    so = pkg.sparse_ops
+    g = torch.Generator(device="cpu").manual_seed(c)
+    feats = torch.randn((5000, c), generator=g).to(dev).to(torch.bfloat16)
+    coords = torch.randint(0, 900, (5000, 4), generator=g, dtype=torch.int32).to(dev)
+    rows = torch.randperm(5000, generator=g)[:1234].to(torch.int32).to(dev)
+    oc, of = so.gather_rows(coords, feats, rows)
+    assert of.dtype == torch.float32 and torch.equal(of, feats.float()[rows.long()]) and torch.equal(oc, coords[rows.long()])
+    mask = torch.zeros(5000, dtype=torch.bool, device=dev)
+    mask[rows.long()] = True
+    oc2, of2 = so.prune_rows_reordered(coords, feats, mask, 1234, reorder=False)          # mask order = ascending source row
+    keep = torch.sort(rows.long()).values
+    assert torch.equal(of2, feats.float()[keep]) and torch.equal(oc2, coords[keep])
+
+
+def test_locality_sort_equals_full_morton_sort_below_4096(pkg, dev):
+    """Sorting on the low 36 Morton bits (12 per axis, 5 radix passes) gives the full (batch, Z-order) permutation for one batch
+    item inside [0, 4096)^3 -- the 10/11-bit frames; outside, it is still a valid permutation (row order is free)."""
+    so = pkg.sparse_ops
+    g = torch.Generator(device="cpu").manual_seed(1)
+    C = torch.cat([torch.zeros((20000, 1), dtype=torch.int32), torch.randint(0, 4096, (20000, 3), generator=g, dtype=torch.int32)], 1).to(dev)
+    assert torch.equal(so.sort_rows_i32(C, morton=True), so.sort_rows_i32(C, morton=True, bits=so.LOCALITY_BITS))
+    far = C.clone()
+    far[:, 1:] += 20000
+    perm = so.sort_rows_i32(far, morton=True, bits=so.LOCALITY_BITS)
+    assert torch.equal(torch.sort(perm.long()).values, torch.arange(20000, device=dev))

@@ -31,6 +31,7 @@ _PROTOS = {
     "pcg_generate_coords": (_I, [_P, _L, _I, _I, _I, _P, _P, _L, _P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_kernel_map": (_I, [_P, _P, _L, _P, _L, _I, _I, _I, _I, _P, _L, _P, _P]),
     "pcg_sort_rows": (_I, [_P, _L, _I, _P, _P, _SZ, _P]),
+    "pcg_sort_rows_bits": (_I, [_P, _L, _I, _I, _I, _P, _P, _SZ, _P]),
     "pcg_sort_rows_scratch_bytes": (_SZ, [_L]),
     "pcg_gather_block": (_I, [_P, _P, _L, _I, _P, _P, _P]),
     "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P]),
@@ -61,6 +62,7 @@ _PROTOS = {
     "pcg_nn_search": (_I, [_P, _P, _L, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P]),
     "pcg_mask_to_rows": (_I, [_P, _L, _P, _P, _P, _SZ, _P]),
     "pcg_gather_rows": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
+    "pcg_gather_rows_bf16": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
     "pcg_color_jitter_scratch_bytes": (_SZ, []),
     "pcg_color_jitter": (_I, [_P, _L, _I, _I, _I, _I, _F, _F, _F, _F, _P, _P, _P]),
     "pcg_rotate_floor": (_I, [_P, _L, _P, _F, _F, _P, _P, _P]),

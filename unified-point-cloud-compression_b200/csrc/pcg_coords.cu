@@ -466,6 +466,26 @@ extern "C" int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, 
 
 // out[r] = src[rows[r]] for r < n_rows: coordinate rows (int32 x 4, src_coords/out_coords optional) and fp32 feature rows of c
 // channels (optional), one warp per row.
+// bf16 source rows (c % 8 == 0 channels, 16-byte aligned rows) -> fp32 output rows: the survivors of a prune whose candidates
+// were only ever written as bf16 (the generative up-sampling emits the operand image of the occupancy head and nothing else)
+__global__ void k_gather_rows_bf16(const int32_t *__restrict__ src_coords, const __nv_bfloat16 *__restrict__ feats, int c,
+                                   const int32_t *__restrict__ rows, long n, int32_t *__restrict__ out_coords, float *__restrict__ out) {
+    long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    long nwarps = ((long)gridDim.x * blockDim.x) >> 5;
+    for (long r = warp; r < n; r += nwarps) {
+        const long sr = rows[r];
+        if (src_coords && lane == 0) reinterpret_cast<int4 *>(out_coords)[r] = pcg_ld_coord(src_coords, sr);
+        const uint4 *src = reinterpret_cast<const uint4 *>(feats + sr * c);
+        float4 *dst = reinterpret_cast<float4 *>(out + r * c);
+        for (int j = lane; j < (c >> 3); j += 32) {          // 8 channels per lane step: one 16-byte load, two 16-byte stores
+            const uint4 v = __ldg(src + j);
+            dst[2 * j] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xFFFF0000u), __uint_as_float(v.y << 16), __uint_as_float(v.y & 0xFFFF0000u));
+            dst[2 * j + 1] = make_float4(__uint_as_float(v.z << 16), __uint_as_float(v.z & 0xFFFF0000u), __uint_as_float(v.w << 16), __uint_as_float(v.w & 0xFFFF0000u));
+        }
+    }
+}
+
 __global__ void k_gather_rows2(const int32_t *__restrict__ src_coords, const float *__restrict__ feats, int c,
                                const int32_t *__restrict__ rows, long n, int32_t *__restrict__ out_coords, float *__restrict__ out) {
     long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -493,6 +513,19 @@ extern "C" int pcg_gather_rows(const int32_t *coords, const float *feats, int c,
     long blocks = cdiv(n_rows * 32, 256);
     if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
     k_gather_rows2<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(coords, feats, c, rows, n_rows, out_coords, out_feats);
+    PCG_LAUNCHED();
+    return 0;
+}
+
+extern "C" int pcg_gather_rows_bf16(const int32_t *coords, const void *feats_bf16, int c, const int32_t *rows, long n_rows,
+                                    int32_t *out_coords, float *out_feats, void *stream) {
+    PCG_CHECK_ARG(n_rows >= 0 && feats_bf16 != nullptr && c >= 8 && (c & 7) == 0, "pcg_gather_rows_bf16: n_rows=%ld c=%d (c must be a multiple of 8)", n_rows, c);
+    PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)out_feats & 15) == 0, "pcg_gather_rows_bf16: rows must be 16-byte aligned");
+    if (n_rows == 0) return 0;
+    long blocks = cdiv(n_rows * 32, 256);
+    if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+    k_gather_rows_bf16<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(coords, reinterpret_cast<const __nv_bfloat16 *>(feats_bf16), c, rows, n_rows,
+                                                                         out_coords, out_feats);
     PCG_LAUNCHED();
     return 0;
 }
@@ -531,10 +564,21 @@ extern "C" size_t pcg_sort_rows_scratch_bytes(long n) {
     return align256(temp) + 2 * align256((size_t)m * 8) + align256((size_t)m * 4) + 256;
 }
 
+extern "C" int pcg_sort_rows_bits(const int32_t *coords, long n, int morton, int begin_bit, int end_bit, int32_t *perm, void *scratch,
+                                  size_t scratch_bytes, void *stream);
 extern "C" int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t *perm, void *scratch, size_t scratch_bytes,
                              void *stream) {
+    return pcg_sort_rows_bits(coords, n, morton, 0, 64, perm, scratch, scratch_bytes, stream);
+}
+
+// Stable sort on key bits [begin_bit, end_bit) only.  Key layout: morton = 0: b:16 | x:16 | y:16 | z:16 (biased by 32768);
+// morton = 1: b:16 | 48 bits of x/y/z interleaved (bit 3 i + 2 = x_i, + 1 = y_i, + 0 = z_i).  A Z-order that only serves
+// memory locality needs the low coordinate bits alone: [0, 36) = 12 bits per axis is 5 radix passes instead of 8.
+extern "C" int pcg_sort_rows_bits(const int32_t *coords, long n, int morton, int begin_bit, int end_bit, int32_t *perm, void *scratch,
+                                  size_t scratch_bytes, void *stream) {
     cudaStream_t st = as_stream(stream);
     if (n <= 0) return 0;
+    PCG_CHECK_ARG(0 <= begin_bit && begin_bit < end_bit && end_bit <= 64, "pcg_sort_rows_bits: bits [%d, %d)", begin_bit, end_bit);
     PCG_CHECK_ARG(scratch && scratch_bytes >= pcg_sort_rows_scratch_bytes(n), "pcg_sort_rows: scratch too small");
     uint8_t *p = reinterpret_cast<uint8_t *>(scratch);
     uint64_t *k_in = reinterpret_cast<uint64_t *>(p); p += align256((size_t)n * 8);
@@ -544,7 +588,7 @@ extern "C" int pcg_sort_rows(const int32_t *coords, long n, int morton, int32_t 
     k_pack_keys<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(coords, n, morton, k_in, i_in);
     PCG_LAUNCHED();
     // plumbing: CUB's radix sort orders the packed 64-bit keys (stable)
-    PCG_CUDA(cub::DeviceRadixSort::SortPairs(p, temp, k_in, k_out, i_in, perm, (int)n, 0, 64, st));
+    PCG_CUDA(cub::DeviceRadixSort::SortPairs(p, temp, k_in, k_out, i_in, perm, (int)n, begin_bit, end_bit, st));
     pcg_launches.fetch_add(1, std::memory_order_relaxed);
     return 0;
 }

@@ -83,7 +83,7 @@ class UnifiedModel(CompressionModel):
         coordinate set (strided / generated, first-occurrence order) inherits the spatial coherence, which is what
         lets a 128-row convolution tile skip the kernel offsets its surface patch does not use."""
         coords0, _ = so.gather_block(x_block)                      # integer coordinates, caller's row order (sort keys only)
-        order = so.sort_rows_i32(coords0, morton=True)
+        order = so.sort_rows_i32(coords0, morton=True, bits=so.LOCALITY_BITS)
         coords4, feats = so.gather_block(x_block, order)           # one pass: Z-ordered coordinates + [1, r, g, b] rows
         uniq, index, table = so.unique_first(coords4)
         if uniq.shape[0] != coords4.shape[0]:

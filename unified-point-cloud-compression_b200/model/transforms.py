@@ -78,7 +78,10 @@ class SparseSynthesisTransform(nn.Module):
         self.prune = ME.MinkowskiPruning()
         self.down_conv = ME.MinkowskiConvolution(in_channels=1, out_channels=1, kernel_size=3, stride=2, dimension=3)
         for up in (self.up_1, self.up_2, self.up_3):
-            up[-1].emit = "both"        # candidates feed the occupancy head (bf16 operand) and the prune (fp32 rows)
+            # the ~20x larger candidate set is written ONCE, as the bf16 operand image the occupancy head reads; the prune turns
+            # the surviving rows back into fp32 (an fp32 copy of every candidate would double the up-sampling kernel's writes
+            # for rows of which 80-90 % are dropped two kernels later).  PCG_CAND_F32=1 restores fp32 + bf16 ("both") for A/B runs.
+            up[-1].emit = "both" if os.environ.get("PCG_CAND_F32") == "1" else "bf16"
 
     # -- helpers -----------------------------------------------------------------------------
     @staticmethod
@@ -108,11 +111,11 @@ class SparseSynthesisTransform(nn.Module):
         if torch.is_grad_enabled() and x.F.requires_grad:
             oc, _ = so.prune_rows(x.C, None, mask, n_keep=n_keep)
             of = x.F[mask]                              # differentiable row gather (training)
-        elif do_reorder and n_keep is not None:
-            oc, of = so.prune_rows_reordered(x.C, x.F, mask, n_keep)      # prune + Z-order in one pass over the feature rows
+        elif n_keep is not None and (do_reorder or x.F.dtype == torch.bfloat16):
+            oc, of = so.prune_rows_reordered(x.C, x.F, mask, n_keep, reorder=do_reorder)      # prune (+ Z-order) in one pass over the feature rows
             return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
         else:
-            oc, of = so.prune_rows(x.C, x.F, mask, n_keep=n_keep)
+            oc, of = so.prune_rows(x.C, x.F.float() if x.F.dtype == torch.bfloat16 else x.F, mask, n_keep=n_keep)
         if do_reorder and oc.shape[0] > 1:
             perm = so.sort_rows(oc, morton=True)
             oc, of = oc[perm].contiguous(), of[perm].contiguous()

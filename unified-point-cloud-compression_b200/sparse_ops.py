@@ -321,8 +321,12 @@ def unique_first(coords):
     return out[:m], index[:m], (keys, vals, cap)
 
 
-def sort_rows_i32(coords, morton=False):
-    """Row permutation (int32): lexicographic (b,x,y,z) (utils.py:142-187) or, with morton=True, (b, Z-order)."""
+LOCALITY_BITS = 36      # Z-order on the low 12 bits per axis: enough for memory locality on 11-bit frames, 5 radix passes instead of 8
+
+
+def sort_rows_i32(coords, morton=False, bits=None):
+    """Row permutation (int32): lexicographic (b,x,y,z) (utils.py:142-187) or, with morton=True, (b, Z-order).
+    bits: sort on the low `bits` key bits only (morton + LOCALITY_BITS: a coherence order for row layouts whose order is free)."""
     _need_cuda(coords, "coordinates")
     coords = coords.to(torch.int32).contiguous()
     n = coords.shape[0]
@@ -330,7 +334,7 @@ def sort_rows_i32(coords, morton=False):
     if n:
         lib = _lib.load()
         ws = scratch(lib.pcg_sort_rows_scratch_bytes(n), coords.device)
-        call("pcg_sort_rows", ptr(coords), n, int(bool(morton)), ptr(perm), ptr(ws), ws.numel(), stream())
+        call("pcg_sort_rows_bits", ptr(coords), n, int(bool(morton)), 0, 64 if bits is None else int(bits), ptr(perm), ptr(ws), ws.numel(), stream())
     return perm
 
 
@@ -806,21 +810,28 @@ def prune_rows(coords, feats, mask, n_keep=None):
 
 
 def gather_rows(coords, feats, rows):
-    """(coords[rows], feats[rows]) for an int32 row list; either input may be None."""
+    """(coords[rows], feats[rows]) for an int32 row list; either input may be None.  feats may be fp32 or bf16 (rows of a
+    multiple of 8 channels, as the up-sampling kernels emit them); the gathered feature rows are always fp32."""
     n = int(rows.shape[0])
     dev = rows.device
     oc = torch.empty((n, 4), dtype=torch.int32, device=dev) if coords is not None else None
     of = torch.empty((n, feats.shape[1]), dtype=torch.float32, device=dev) if feats is not None else None
-    row_bytes = (16 if coords is not None else 0) + (4 * feats.shape[1] if feats is not None else 0)
-    with hbm_span("gather_rows", (n, row_bytes), (4.0 + 2.0 * row_bytes) * n):        # row list + rows read + rows written
-        call("pcg_gather_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, feats.shape[1] if feats is not None else 0,
-             ptr(rows), n, ptr(oc), ptr(of), stream())
+    src_bytes = 0 if feats is None else feats.element_size() * feats.shape[1]
+    row_in = (16 if coords is not None else 0) + src_bytes
+    row_out = (16 if coords is not None else 0) + (4 * feats.shape[1] if feats is not None else 0)
+    with hbm_span("gather_rows", (n, row_in), (4.0 + row_in + row_out) * n):        # row list + rows read + rows written
+        if feats is not None and feats.dtype == torch.bfloat16:
+            call("pcg_gather_rows_bf16", ptr(coords), ptr(feats.contiguous()), feats.shape[1], ptr(rows), n, ptr(oc), ptr(of), stream())
+        else:
+            call("pcg_gather_rows", ptr(coords), ptr(feats.contiguous()) if feats is not None else None, feats.shape[1] if feats is not None else 0,
+                 ptr(rows), n, ptr(oc), ptr(of), stream())
     return oc, of
 
 
-def prune_rows_reordered(coords, feats, mask, n_keep):
+def prune_rows_reordered(coords, feats, mask, n_keep, reorder=True):
     """Rows under `mask` in (batch, Z-order) order: the prune (ME.MinkowskiPruning) composed with the Z-order re-sort of the
-    survivors.  The feature rows move once: kept-row list -> Morton permutation of the kept coordinates -> one gather."""
+    survivors.  The feature rows move once: kept-row list -> Morton permutation of the kept coordinates -> one gather.
+    reorder=False: mask order kept (the plain prune, for bf16 candidate rows: the gather converts the survivors to fp32)."""
     n = mask.shape[0]
     dev = mask.device
     m8 = mask.view(torch.uint8) if mask.dtype == torch.bool else mask.to(torch.uint8)
@@ -831,9 +842,11 @@ def prune_rows_reordered(coords, feats, mask, n_keep):
     ws = scratch(lib.pcg_scratch_bytes(max(n, 1)), dev)
     call("pcg_mask_to_rows", ptr(m8.contiguous()), n, ptr(rows), ptr(cnt), ptr(ws), ws.numel(), stream())
     rows = rows[:n_keep]
+    if not reorder:
+        return gather_rows(coords, feats, rows)
     oc, _ = gather_rows(coords, None, rows)
     if n_keep > 1:
-        perm = sort_rows_i32(oc, morton=True)
+        perm = sort_rows_i32(oc, morton=True, bits=LOCALITY_BITS)
         rows = torch.index_select(rows, 0, perm)
     return gather_rows(coords, feats, rows)
 
