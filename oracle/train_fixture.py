@@ -71,11 +71,19 @@ def main(steps=400, width=32, lr=1e-3):
         q, lam = q_func(x)
         out = net(x, q, lam)
         loss, parts = loss_fn(x, out)
-        if not torch.isfinite(loss):           # (the reference's ColorLoss is the mean of an EMPTY tensor = NaN when no predicted voxel lies on the
-            print(f"step {step:4d} skipped: non-finite loss", flush=True)      # ground truth, loss.py:95-111; its train.py has no guard -- this driver skips the step)
-            continue
+        if not torch.isfinite(loss):
+            # the reference's ColorLoss is the mean of an EMPTY tensor (= NaN) when no predicted voxel lies on the ground truth
+            # (loss.py:95-111) and its train.py has no guard; this driver then steps on the finite terms (geometry + rate) only
+            finite = [v for v in parts.values() if torch.isfinite(v)]
+            if not finite:
+                print(f"step {step:4d} skipped: no finite loss term", flush=True)
+                continue
+            loss = sum(finite)
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(net.parameters(), cfg_all["clip_grad_norm"])
+        gn = torch.nn.utils.clip_grad_norm_(net.parameters(), cfg_all["clip_grad_norm"])
+        if not torch.isfinite(gn):
+            print(f"step {step:4d} skipped: non-finite gradient", flush=True)
+            continue
         opt.step()
         aux = net.aux_loss()
         aux.backward()
