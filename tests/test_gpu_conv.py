@@ -372,3 +372,65 @@ def test_conv_transpose_onto_given_coordinates_matches_oracle(pkg, dev, cin, cou
         if stride > 1:
             with pytest.raises(RuntimeError):
                 conv(x, wrong)                                           # wrong tensor stride
+
+
+@pytest.mark.parametrize("cin,cout,ksize,stride,transposed", [(128, 128, 3, 1, False), (128, 128, 5, 2, False), (192, 256, 3, 1, False),
+                                                              (192, 192, 2, 2, True), (128, 32, 5, 2, True), (64, 16, 3, 1, False),
+                                                              (128, 64, 3, 1, False), (40, 48, 3, 1, False), (128, 192, 3, 1, False)])
+def test_weight_gradient_on_tensor_cores(pkg, dev, cin, cout, ksize, stride, transposed):
+    """pcg_conv_bwd_weight_tc (tcgen05, MN-major operands taken from the gathered row tiles, sliced + fixed-order reduction):
+    bit-exact against the fp32 kernel on integer-valued operands (pins the MN-major descriptors / swizzle / TMEM lane mapping),
+    <= 1e-2 relative L2 on random operands (bf16 rounding of F and G), and bit-reproducible run to run; then the same through
+    autograd in "auto" mode (forward on the tensor cores, input gradient on the inverse map, weight gradient by this kernel)."""
+    so = pkg.sparse_ops
+    ag = importlib.import_module(pkg.__name__ + ".autograd")
+    lib = pkg._lib.load()
+    from importlib import import_module
+    L = import_module(pkg.__name__ + "._lib")
+    ts = 2 if transposed else 1
+    C, cs = setup(dev, pkg, seed=cin + 3 * cout, ts=ts, scale=2)
+    out_set = cs.generated(ksize, stride) if transposed else cs.strided(stride)
+    K = ksize ** 3
+    assert ag.bwd_weight_tc_eligible(K, cin, cout)
+    nbr, tmask = cs.kernel_map(out_set, ksize, transposed)
+    rng = np.random.default_rng(cin + cout)
+
+    def both(Fm, G):
+        Fd, Gd = torch.from_numpy(Fm).to(dev), torch.from_numpy(G).to(dev)
+        ref = torch.empty((K, cin, cout), device=dev)
+        L.call("pcg_conv_bwd_weight_f32", L.ptr(Fd), cin, L.ptr(nbr), nbr.shape[1], L.ptr(tmask), K, out_set.n, L.ptr(Gd), cout, L.ptr(ref), L.stream())
+        fb = so.to_bf16(Fd)
+        cp = (cout + 63) // 64 * 64
+        gb = torch.empty((out_set.n, cp), dtype=torch.bfloat16, device=dev)
+        L.call("pcg_f32_to_bf16_rows", L.ptr(Gd), out_set.n, cout, cp, L.ptr(gb), L.stream())
+        ws = torch.empty(lib.pcg_conv_bwd_weight_tc_scratch_bytes(K, cin, cout, out_set.n), dtype=torch.uint8, device=dev)
+        outs = []
+        for _ in range(2):
+            dw = torch.full((K, cin, cout), float("nan"), device=dev)
+            L.call("pcg_conv_bwd_weight_tc", L.ptr(fb), cin, L.ptr(gb), cout, L.ptr(nbr), nbr.shape[1], L.ptr(tmask), K, out_set.n,
+                   L.ptr(ws), ws.numel(), L.ptr(dw), L.stream())
+            outs.append(dw)
+        assert torch.equal(outs[0], outs[1]), "not reproducible"
+        return ref, outs[0]
+
+    ref, got = both(rng.integers(-3, 4, (cs.n, cin)).astype(np.float32), rng.integers(-2, 3, (out_set.n, cout)).astype(np.float32))
+    assert torch.isfinite(got).all() and float(ref.abs().max()) > 0
+    assert torch.equal(ref, got), f"integer operands: max |d| = {float((ref - got).abs().max())}"
+    ref, got = both(rng.standard_normal((cs.n, cin)).astype(np.float32), rng.standard_normal((out_set.n, cout)).astype(np.float32))
+    err = rel_l2(got.cpu().numpy(), ref.cpu().numpy())
+    assert err < 1e-2, f"random operands: rel-L2 {err:.3e}"
+    # through autograd, tensor-core mode end to end
+    Fm = torch.from_numpy(rng.standard_normal((cs.n, cin)).astype(np.float32))
+    W = torch.from_numpy((rng.standard_normal((K, cin, cout)) / np.sqrt(cin * K) * 3).astype(np.float32))
+    G = torch.from_numpy(rng.standard_normal((out_set.n, cout)).astype(np.float32))
+    grads = {}
+    for mode in ("f32", "auto"):
+        prev = so.set_conv_mode(mode)
+        try:
+            Fd, Wd = Fm.clone().to(dev).requires_grad_(True), W.clone().to(dev).requires_grad_(True)
+            out = ag.sparse_conv_autograd(Fd, cs, out_set, Wd, None, ksize, transposed, so.ACT_LEAKY)
+            (out * G.to(dev)).sum().backward()
+            grads[mode] = (Fd.grad.cpu().numpy(), Wd.grad.cpu().numpy())
+        finally:
+            so.set_conv_mode(prev)
+    assert rel_l2(grads["auto"][0], grads["f32"][0]) < 1.5e-2 and rel_l2(grads["auto"][1], grads["f32"][1]) < 1.5e-2

@@ -15,6 +15,12 @@ from . import sparse_ops as so
 from ._lib import call, ptr, stream
 
 
+def bwd_weight_tc_eligible(K, cin, cout):
+    """Static rule for the tensor-core weight gradient (pcg_conv_bwd_weight_tc): every layer of the model at its configured widths
+    except the 4-channel input layer, the narrow occupancy-head layers and the 1x1 colour head, which keep the fp32 kernel."""
+    return so.get_conv_mode() != "f32" and K <= 128 and 33 <= cin <= 256 and 16 <= cout <= 256 and ((cin + 127) // 128) * ((cout + 15) // 16 * 16) <= 512
+
+
 def _act_grad(gout, out, act):
     if act == so.ACT_RELU:
         return gout * (out > 0).to(gout.dtype)
@@ -46,8 +52,19 @@ class _SparseConv(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             nbr, tmask = in_set.kernel_map(out_set, ksize, transposed)
             dw = torch.empty_like(w3)
-            call("pcg_conv_bwd_weight_f32", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n, ptr(g), cout,
-                 ptr(dw), stream())
+            if bwd_weight_tc_eligible(K, cin, cout) and tmask is not None and out_set.n > 0 and feats.shape[0] > 0:
+                # tensor cores: bf16 operand rows of F (cached shadow of the forward pass when there is one) and of G
+                fb = so.to_bf16(feats)
+                cp = (cout + 63) // 64 * 64
+                gb = torch.empty((g.shape[0], cp), dtype=torch.bfloat16, device=g.device)
+                call("pcg_f32_to_bf16_rows", ptr(g), g.shape[0], cout, cp, ptr(gb), stream())
+                lib = so._lib.load()
+                ws = so.scratch(lib.pcg_conv_bwd_weight_tc_scratch_bytes(K, cin, cout, out_set.n), g.device)
+                call("pcg_conv_bwd_weight_tc", ptr(fb), cin, ptr(gb), cout, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n,
+                     ptr(ws), ws.numel(), ptr(dw), stream())
+            else:
+                call("pcg_conv_bwd_weight_f32", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n, ptr(g), cout,
+                     ptr(dw), stream())
             g_weight = dw.view_as(weight)
         if has_bias and ctx.needs_input_grad[2]:
             g_bias = g.sum(dim=0, keepdim=True)

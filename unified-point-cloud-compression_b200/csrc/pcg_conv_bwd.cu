@@ -59,3 +59,245 @@ extern "C" int pcg_conv_bwd_weight_f32(const float *feats, int cin, const int32_
     PCG_LAUNCHED();
     return 0;
 }
+
+// ---------------------------------------------------------------------------- weight gradient on the tensor cores
+// dW[k] = F_k^T . G with F_k = the gathered input rows of offset k (absent neighbours = zero rows): per offset a GEMM whose
+// REDUCTION dimension is the row index.  tcgen05 takes both operands "MN-major" for that (instruction-descriptor bits 15 / 16):
+// the canonical SWIZZLE_128B MN-major tile is rows (reduction index) of 128 bytes = 64 channels, 8-row groups 1024 bytes apart,
+// 64-channel blocks LBO apart -- byte for byte the image the forward kernel's LSU gather writes for a 64-channel chunk of 128
+// rows.  So the producers of k_conv_tc_mt are reused unchanged: per 128-row tile they gather cin_p/64 chunk images of F (through
+// nbr[k]) and cout_p/64 chunk images of G (identity rows), and one thread issues, per 16 rows, MMAs of M = 128 input channels x
+// N = cout into fp32 accumulators in TMEM (one per block of 128 input channels).
+// CTA (k, s) walks the tiles of slice s in ascending order (tiles whose mask bit k is clear are skipped) and writes its partial
+// [cin][cout] block; k_bwd_reduce_partials then adds the slices in ascending order: one fixed summation order per element, no
+// atomics (same determinism argument as the forward path).
+#include "pcg_tc.cuh"
+
+#define BWT_ROWS 128
+#define BWT_CHUNK_BYTES (BWT_ROWS * 128)       // one 64-channel chunk image of a 128-row tile
+#define BWT_MAX_STAGES 4
+
+struct BwtParams {
+    const uint8_t *feats;        // bf16 [n_in][cin_p]
+    const uint8_t *gout;         // bf16 [n_out][cout_p]
+    const int32_t *nbr;          // [K][pitch]
+    const uint32_t *tile_mask;   // [tiles][4]
+    float *partial;              // [S][K][cin][cout]
+    long n_out, pitch, tiles, tiles_per_slice;
+    int cin, cout, K;
+    int ci_chunks;               // 64-channel chunks of F actually present (cin_p / 64)
+    int ci_chunks_p;             // rounded up to a multiple of 2 (blocks of M = 128; the padding chunk is zero-filled)
+    int co_chunks;               // cout_p / 64
+    int n_mma;                   // N of the instruction = roundup16(cout)
+    int stages, tmem_cols;
+};
+
+// MN-major SWIZZLE_128B shared-memory matrix descriptor: 64-element blocks along M/N `lbo` bytes apart, 8-row groups along the
+// reduction dimension 1024 bytes apart
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t saddr, uint32_t lbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+__global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t *sm = smem_raw + (base - raw);
+    const int n_chunks = p.ci_chunks_p + p.co_chunks;              // chunk images per stage: F chunks first, then G chunks
+    const uint32_t stage_bytes = (uint32_t)n_chunks * BWT_CHUNK_BYTES;
+    uint8_t *ctl = sm + (size_t)p.stages * stage_bytes;
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(ctl);
+    uint64_t *empty_bar = full_bar + BWT_MAX_STAGES;
+    uint64_t *accum_bar = empty_bar + BWT_MAX_STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_bar + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int k = blockIdx.x;
+    const long t0 = (long)blockIdx.y * p.tiles_per_slice;
+    const long t1 = t0 + p.tiles_per_slice < p.tiles ? t0 + p.tiles_per_slice : p.tiles;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(smem_u32(full_bar + s), 32 * n_chunks);      // one cp.async-completion arrive per lane and chunk image
+            mbar_init(smem_u32(empty_bar + s), 1);
+        }
+        mbar_init(smem_u32(accum_bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_d = *tmem_slot;
+    auto active = [&](long t) -> bool { return (__ldg(p.tile_mask + t * 4 + (k >> 5)) >> (k & 31)) & 1u; };
+    const int m_blocks = p.ci_chunks_p / 2;
+
+    if (warp < 4) {
+        // ------------------------------------------------------------------ producers: warp w gathers chunk images w, w+4, ...
+        const int row_f = p.ci_chunks * 128, row_g = p.co_chunks * 128;       // bytes per source row
+        const uint8_t *fsrc = p.feats + (lane & 7) * 16, *gsrc = p.gout + (lane & 7) * 16;
+        int s = 0;
+        uint32_t wrap = 0;
+        for (long t = t0; t < t1; ++t) {
+            if (!active(t)) continue;                                          // warp-uniform
+            int idx_f[4], idx_g[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long o = t * BWT_ROWS + lane + 32 * u;
+                idx_f[u] = __ldg(p.nbr + (long)k * p.pitch + o);               // the table is padded with -1 to a multiple of 128 rows
+                idx_g[u] = (o < p.n_out && idx_f[u] >= 0) ? (int)o : -1;
+            }
+            const uint32_t fb = smem_u32(full_bar + s);
+            const uint32_t st_base = base + (uint32_t)s * stage_bytes;
+            mbar_wait(smem_u32(empty_bar + s), (wrap & 1u) ^ 1u);
+            for (int c = warp; c < n_chunks; c += 4) {
+                const uint32_t dst = st_base + (uint32_t)c * BWT_CHUNK_BYTES;
+                if (c < p.ci_chunks) tc_lsu_gather_tile<128, false>(dst, fsrc + c * 128, row_f, idx_f, lane);
+                else if (c < p.ci_chunks_p) {                                   // zero padding chunk of the last 128-channel block
+                    const int none[4] = {-1, -1, -1, -1};
+                    tc_lsu_gather_tile<128, false>(dst, fsrc, row_f, none, lane);
+                } else tc_lsu_gather_tile<128, false>(dst, gsrc + (c - p.ci_chunks_p) * 128, row_g, idx_g, lane);
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
+            }
+            if (++s == p.stages) { s = 0; ++wrap; }
+        }
+    } else if (lane == 0) {
+        // ------------------------------------------------------------------ MMA issuer
+        // idesc: fp32 accumulate, bf16 x bf16, A and B MN-major (bits 15 / 16), N, M = 128
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.n_mma >> 3) << 17) | ((128u >> 4) << 24);
+        int s = 0;
+        uint32_t ph = 0, started = 0;
+        for (long t = t0; t < t1; ++t) {
+            if (!active(t)) continue;
+            mbar_wait(smem_u32(full_bar + s), ph);
+            fence_proxy_async();                      // cp.async wrote the images through the generic proxy
+            tc_fence_after();
+            const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+            const uint32_t b_base = a_base + (uint32_t)p.ci_chunks_p * BWT_CHUNK_BYTES;
+            for (int mb = 0; mb < m_blocks; ++mb) {
+#pragma unroll
+                for (int kk = 0; kk < BWT_ROWS / 16; ++kk) {             // 16 rows (two 8-row groups = 2048 bytes) per instruction
+                    const uint64_t adesc = umma_desc_mn_sw128(a_base + (uint32_t)(2 * mb) * BWT_CHUNK_BYTES + kk * 2048, BWT_CHUNK_BYTES);
+                    const uint64_t bdesc = umma_desc_mn_sw128(b_base + kk * 2048, BWT_CHUNK_BYTES);
+                    umma_bf16(tmem_d + (uint32_t)(mb * p.n_mma), adesc, bdesc, idesc, (started | (uint32_t)kk) ? 1u : 0u);
+                }
+            }
+            started = 1u;
+            umma_commit(smem_u32(empty_bar + s));
+            if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+        if (started) umma_commit(smem_u32(accum_bar));
+        *reinterpret_cast<volatile uint32_t *>(tmem_slot + 1) = started;       // read by the epilogue after the barrier below
+    }
+    __syncwarp();
+    __syncthreads();
+    const uint32_t any = *reinterpret_cast<volatile uint32_t *>(tmem_slot + 1);
+    if (warp < 4) {
+        // ------------------------------------------------------------------ epilogue: thread = input channel (TMEM lane) of each 128-channel block
+        if (any) {
+            mbar_wait(smem_u32(accum_bar), 0);
+            tc_fence_after();
+        }
+        float *dst_k = p.partial + ((size_t)blockIdx.y * p.K + k) * (size_t)p.cin * p.cout;
+        for (int mb = 0; mb < m_blocks; ++mb) {
+            const int ci = mb * 128 + tid;
+            const uint32_t lane_base = tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mb * p.n_mma);
+            for (int c0 = 0; c0 < p.cout; c0 += 16) {
+                uint32_t v[16];
+                if (any) tmem_ld16(lane_base + (uint32_t)c0, v);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = 0u;
+                }
+                if (ci < p.cin) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (c0 + j < p.cout) dst_k[(size_t)ci * p.cout + c0 + j] = __uint_as_float(v[j]);
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)p.tmem_cols) : "memory");
+    }
+}
+
+// dw[i] = sum_s partial[s][i], s ascending
+__global__ void k_bwd_reduce_partials(const float *__restrict__ partial, int slices, long n, float *__restrict__ dw) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        float acc = 0.f;
+        for (int s = 0; s < slices; ++s) acc += __ldg(partial + (long)s * n + i);
+        dw[i] = acc;
+    }
+}
+
+static long bwt_slices(int K, long tiles) {
+    long s = cdiv(2L * PCG_SMS, K);          // about two waves of CTAs (one CTA per SM: the operand ring takes most of the shared memory)
+    if (s > tiles) s = tiles;
+    if (s > 64) s = 64;
+    return s < 1 ? 1 : s;
+}
+
+extern "C" size_t pcg_conv_bwd_weight_tc_scratch_bytes(int K, int cin, int cout, long n_out) {
+    const long tiles = cdiv(n_out > 0 ? n_out : 1, BWT_ROWS);
+    return (size_t)bwt_slices(K, tiles) * K * cin * cout * sizeof(float) + 256;
+}
+
+extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const void *gout_bf16, int cout, const int32_t *nbr, long nbr_pitch,
+                                      const uint32_t *tile_mask, int K, long n_out, void *scratch, size_t scratch_bytes, float *dweight,
+                                      void *stream) {
+    PCG_CHECK_ARG(K >= 1 && K <= 128, "pcg_conv_bwd_weight_tc: K=%d must be in [1,128] (tile mask)", K);
+    PCG_CHECK_ARG(cin >= 33 && cin <= 256 && cout >= 1 && cout <= 256, "pcg_conv_bwd_weight_tc: cin=%d (33..256) cout=%d (1..256)", cin, cout);
+    PCG_CHECK_ARG(tile_mask != nullptr && (nbr_pitch & 127) == 0 && nbr_pitch >= n_out, "pcg_conv_bwd_weight_tc: tile_mask / padded neighbour table required");
+    PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)gout_bf16 & 15) == 0, "pcg_conv_bwd_weight_tc: operands must be 16-byte aligned");
+    cudaStream_t st = as_stream(stream);
+    const long n_w = (long)K * cin * cout;
+    if (n_out <= 0) {
+        PCG_CUDA(cudaMemsetAsync(dweight, 0, (size_t)n_w * sizeof(float), st));
+        return 0;
+    }
+    BwtParams p;
+    p.feats = reinterpret_cast<const uint8_t *>(feats_bf16); p.gout = reinterpret_cast<const uint8_t *>(gout_bf16);
+    p.nbr = nbr; p.tile_mask = tile_mask; p.pitch = nbr_pitch; p.n_out = n_out;
+    p.tiles = cdiv(n_out, BWT_ROWS);
+    const long slices = bwt_slices(K, p.tiles);
+    p.tiles_per_slice = cdiv(p.tiles, slices);
+    p.cin = cin; p.cout = cout; p.K = K;
+    p.ci_chunks = (cin + 63) / 64; p.ci_chunks_p = (p.ci_chunks + 1) & ~1; p.co_chunks = (cout + 63) / 64;
+    p.n_mma = (cout + 15) & ~15;
+    const int cols = (p.ci_chunks_p / 2) * p.n_mma;
+    PCG_CHECK_ARG(cols <= 512, "pcg_conv_bwd_weight_tc: cin=%d x cout=%d needs %d TMEM columns (> 512)", cin, cout, cols);
+    p.tmem_cols = 32;
+    while (p.tmem_cols < cols) p.tmem_cols <<= 1;
+    const size_t stage_bytes = (size_t)(p.ci_chunks_p + p.co_chunks) * BWT_CHUNK_BYTES;
+    int stages = (int)((208 * 1024) / stage_bytes);
+    PCG_CHECK_ARG(stages >= 1, "pcg_conv_bwd_weight_tc: one stage of %zu bytes does not fit in shared memory", stage_bytes);
+    if (stages > BWT_MAX_STAGES) stages = BWT_MAX_STAGES;
+    p.stages = stages;
+    PCG_CHECK_ARG(scratch && scratch_bytes >= (size_t)slices * n_w * sizeof(float), "pcg_conv_bwd_weight_tc: scratch too small");
+    p.partial = reinterpret_cast<float *>(scratch);
+    const size_t smem = 1024 + (size_t)stages * stage_bytes + 256;
+    PCG_CUDA(cudaFuncSetAttribute(k_conv_bwd_weight_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_conv_bwd_weight_tc<<<dim3((unsigned)K, (unsigned)slices), 160, smem, st>>>(p);
+    PCG_LAUNCHED();
+    long blocks = cdiv(n_w, 256);
+    if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+    k_bwd_reduce_partials<<<(unsigned)blocks, 256, 0, st>>>(p.partial, (int)slices, n_w, dweight);
+    PCG_LAUNCHED();
+    return 0;
+}

@@ -129,6 +129,51 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// LSU gather of one 128-row x 128-byte operand sub-tile into its 128B-swizzled image at dst_tile.  Lane m holds the neighbour
+// indices of rows m, 32+m, 64+m, 96+m in idx[0..3]; a warp instruction copies rows 4j..4j+3 (8 lanes x 16 B each).  A producer
+// warp is alone on its scheduler, so every instruction costs its full latency: the copy is kept to shuffle + compare + one
+// 32x32->64 multiply-add + cp.async (absent rows: src-size 0 zero-fills and the source address is never dereferenced; the
+// destination offsets are two per-lane constants + immediates since (row & 7) = 4 (u & 1) + q).
+__device__ __forceinline__ int tc_shfl_idx(int v, int src_lane) {      // volatile: keeps the batch order written below
+    int r;
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(v), "r"(src_lane));
+    return r;
+}
+template <int RB, bool CA>
+__device__ __forceinline__ void tc_lsu_gather_tile(uint32_t dst_tile, const uint8_t *fcol, int row_bytes, const int (&idx)[4], int lane) {
+    // rows of RB bytes: LPR lanes per row, RPI rows per warp instruction.  fcol already points at this lane's 16-byte chunk of
+    // the operand columns.  Swizzle of the destination chunk: RB 128: c ^ (r & 7), 64: c ^ ((r >> 1) & 3), 32: c ^ ((r >> 2) & 1);
+    // with r = j*RPI + q the term depends on j only for RB = 128 (two per-lane constants), not at all for 64 / 32.
+    constexpr int LPR = RB / 16, RPI = 32 / LPR, NI = 128 / RPI;
+    const int q = lane / LPR, c16 = lane % LPR;
+    uint32_t d0, d1;
+    if (RB == 128) {
+        d0 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ q) << 4);
+        d1 = dst_tile + (uint32_t)q * 128u + (uint32_t)((c16 ^ (4 + q)) << 4);
+    } else {
+        const int x = RB == 64 ? ((q >> 1) & 3) : ((q >> 2) & 1);
+        d0 = d1 = dst_tile + (uint32_t)q * RB + (uint32_t)((c16 ^ x) << 4);
+    }
+    asm volatile("" : "+l"(fcol));        // keep the column base one 64-bit addend of the multiply-add below
+#pragma unroll
+    for (int jb = 0; jb < NI / 8; ++jb) {
+        int src[8];                       // eight shuffles in flight, then eight copies: the latencies overlap instead of adding up
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int r0 = (8 * jb + u) * RPI;                      // first row of this instruction; row = r0 + q
+            src[u] = tc_shfl_idx(idx[r0 >> 5], (r0 & 31) + q);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int r0 = (8 * jb + u) * RPI;
+            const uint32_t dst = ((RB == 128 && (u & 1)) ? d1 : d0) + (uint32_t)(r0 * RB);
+            const uint8_t *from = fcol + (unsigned long long)(unsigned)src[u] * (unsigned)row_bytes;
+            if (CA) cp_async16_ca(dst, from, src[u] >= 0 ? 16u : 0u);
+            else cp_async16(dst, from, src[u] >= 0 ? 16u : 0u);
+        }
+    }
+}
+
 typedef CUresult (*PcgEncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
