@@ -56,3 +56,47 @@ def test_q_to_lambda_map():
     assert torch.allclose(lam, torch.tensor([[0.5, 2.1], [1.25, 0.225]]))
     lam = tr.scale_q_vals(q, "exponential", a_G=2.0, b_G=0.0, a_A=1.0, b_A=1.0)
     assert torch.allclose(lam, torch.tensor([[1.0, 3.0], [2.0, 2 ** 0.25 + 1.0]]))
+
+
+def _hook_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(6, 40), torch.nn.Tanh(), torch.nn.Linear(40, 40), torch.nn.Tanh(), torch.nn.Linear(40, 3))
+    unused = torch.nn.Parameter(torch.zeros(5))                     # a parameter the loss does not reach (e.g. rescale_nn)
+    params = list(net.parameters()) + [unused]
+    buckets = _training().GradBuckets(params, world, bucket_bytes=1000)       # several buckets
+    x = torch.randn(16, 6, generator=torch.Generator().manual_seed(100 + rank))
+    for _ in range(2):                                              # hooks re-arm every step
+        for p in params:
+            p.grad = None
+        buckets.start()
+        net(x).pow(2).sum().backward()                              # all-reduces are launched from the hooks during this call
+        n = buckets.finish()
+    if rank == 0:
+        torch.save({"grads": [p.grad for p in net.parameters()], "n": n, "n_buckets": len(buckets.buckets), "unused": unused.grad}, out)
+    dist.destroy_process_group()
+
+
+def test_overlapped_gradient_buckets_equal_the_mean(tmp_path):
+    """GradBuckets (post-accumulate-grad hooks, asynchronous bucket all-reduce launched during backward) over a world_size-2
+    gloo group: every gradient ends as the mean over the ranks; a parameter without gradient does not stall its bucket."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = str(tmp_path / "h.pt")
+    mp.spawn(_hook_worker, args=(2, port, out), nprocs=2, join=True)
+    got = torch.load(out)
+    assert got["n_buckets"] >= 2 and got["n"] >= 2 and got["unused"] is None
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(6, 40), torch.nn.Tanh(), torch.nn.Linear(40, 40), torch.nn.Tanh(), torch.nn.Linear(40, 3))
+    want = None
+    for rank in range(2):
+        for p in net.parameters():
+            p.grad = None
+        x = torch.randn(16, 6, generator=torch.Generator().manual_seed(100 + rank))
+        net(x).pow(2).sum().backward()
+        g = [p.grad.clone() for p in net.parameters()]
+        want = g if want is None else [a + b for a, b in zip(want, g)]
+    for g, w in zip(got["grads"], want):
+        assert torch.allclose(g, w / 2, atol=1e-6)
