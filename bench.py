@@ -146,7 +146,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
-    ap.add_argument("--workload", default="frame10", choices=["frame10", "block128", "frame11"])
+    ap.add_argument("--workload", default="frame10", choices=["frame10", "block128", "frame11", "stream11", "train256"],
+                    help="frame10: BASELINE configs[1] (default, the metric's config); block128: configs[0]; stream11: configs[2], 64-frame 11-bit "
+                         "stream sharded by frame (strong scaling); train256: configs[3], the training step on 256^3 blocks, batch 8 per GPU")
+    ap.add_argument("--frames", type=int, default=64, help="stream11: frames in the sequence")
+    ap.add_argument("--topk-from", default="decoder", choices=["decoder", "encoder"],
+                    help="encoder: prune every decoder level with the TRUE occupancy (what a trained model's top-k selects) instead of the "
+                         "random-init logits, which keep a scattered set and make levels 2/3 ~1.5x heavier than any deployment sees")
     ap.add_argument("--conv-mode", default="auto", choices=["auto", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--in-flight", type=int, default=2, help="frames in flight per GPU (host threads x CUDA streams); 1 = single stream")
@@ -201,6 +207,13 @@ def main():
     net = model_mod.UnifiedModel(model_config()).to(dev).eval()
     net.update()
     q = torch.tensor([[0.5, 0.5]], device=dev)
+    if args.workload in ("stream11", "train256"):
+        ctx = argparse.Namespace(args=args, rank=rank, world=world, dev=dev, pkg=pkg, net=net, q=q, emit=emit, config=config)
+        (run_stream if args.workload == "stream11" else run_train)(ctx)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    net.g_s.topk_from_encoder = args.topk_from == "encoder"
 
     depth = max(1, args.in_flight)
     # a step codes `depth` frames (one per worker stream): frame seeds rank, rank + world, ...
@@ -216,7 +229,7 @@ def main():
         dev_cloud = dev_clouds[j]
         enc = net.encode_block(dev_cloud, q)
         ys = enc["y_symbols"]
-        x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], q)
+        x_hat = net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], q, keep_sets=enc.get("keep_sets"))
         return net.finalize(x_hat.C, x_hat.F)
 
     io_frame = {}                                        # frame slot -> (h2d bytes, d2h bytes) of one step
@@ -240,7 +253,7 @@ def main():
         torch.cuda.current_stream().synchronize()
         # (host range coder runs here in a deployment; excluded by the metric)
         yp, zs, ys = (host[k].to(dev, non_blocking=True) for k in ("y_points", "z_symbols", "y_symbols"))
-        x_hat = net.decode_block(yp, zs, lambda idx: ys, enc["k"], q)
+        x_hat = net.decode_block(yp, zs, lambda idx: ys, enc["k"], q, keep_sets=enc.get("keep_sets"))
         rec = to_host("rec", net.finalize(x_hat.C, x_hat.F), j)
         torch.cuda.current_stream().synchronize()
         io_frame[j] = (x.numel() * 4 + sum(host[k].numel() * host[k].element_size() for k in ("y_points", "z_symbols", "y_symbols")),
@@ -393,7 +406,8 @@ def main():
             "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
             "config": dict(config, points_per_step=n_points, frames_per_step=depth,
                            in_flight=f"{depth} frame(s) in flight per GPU: {depth} host thread(s) x CUDA stream(s) (codec.FramePipeline)",
-                           l2="512 MiB flush buffer written between timed steps", conv_mode=args.conv_mode),
+                           l2="512 MiB flush buffer written between timed steps", conv_mode=args.conv_mode,
+                           topk_from=args.topk_from + (" (measurement switch: every decoder level pruned with the true occupancy)" if args.topk_from == "encoder" else "")),
             "clocks": clk,
             "e2e": {"value": total_points / (ms_e2e * 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": sum(v[0] for v in io_frame.values()), "d2h_bytes_per_step": sum(v[1] for v in io_frame.values())},
@@ -410,6 +424,240 @@ def main():
         pipe.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+# ----------------------------------------------------------------------------------------- helpers shared by the extra workloads
+def _reduce(ctx, v, op):
+    import torch
+    import torch.distributed as dist
+    if ctx.world == 1:
+        return float(v)
+    t = torch.tensor([float(v)], device=ctx.dev, dtype=torch.float64)
+    dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+    return float(t.item())
+
+
+def _barrier(ctx):
+    import torch
+    import torch.distributed as dist
+    if ctx.world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+# ----------------------------------------------------------------------------------------- configs[2]: the sharded 11-bit stream
+def stream_frames(n_frames, n_base=4):
+    """64-frame 11-bit Owlii-shaped sequence (SURVEY.md 8d): `n_base` generated frames (oracle/synth.py::frame11, seeds 0..n_base-1,
+    ~2.5 M voxels each; sampling 47 M surface points per frame on the host is ~15 s, hence not 64 of them) x integer translations
+    of up to +-8 voxels.  Returns (loader(i) -> (N,6) float32 numpy, sizes)."""
+    import numpy as np
+    bases = [make_frame("frame11", seed=s) for s in range(min(n_base, n_frames))]
+    rng = np.random.default_rng(11)
+    shifts = rng.integers(-8, 9, size=(n_frames, 3))
+
+    def load(i):
+        p, c = bases[i % len(bases)]
+        return np.concatenate([(p + shifts[i]).astype(np.float32), c], axis=1)
+    return load, [len(bases[i % len(bases)][0]) for i in range(n_frames)]
+
+
+def run_stream(ctx):
+    """Strong scaling: the SAME n frames whatever the number of ranks; frames assigned largest-first (codec.lpt_schedule), each rank
+    codes its frames through codec.StreamCodec at block_size 512 (evaluate.py:45: 6-8 blocks per 11-bit frame), two frames in
+    flight, no collective on the data path; results (voxel counts + a checksum per frame) gathered on rank 0."""
+    import numpy as np
+    import torch
+    args, dev, pkg, net, rank, world = ctx.args, ctx.dev, ctx.pkg, ctx.net, ctx.rank, ctx.world
+    codec_mod = importlib.import_module(pkg.__name__ + ".codec")
+    n_frames = args.frames
+    load, sizes = stream_frames(n_frames)
+    mine = codec_mod.my_units(sizes, world, rank)
+    host = {i: torch.from_numpy(load(i)).pin_memory() for i in mine}
+    resident = {i: h.to(dev) for i, h in host.items()}
+    depth = max(1, args.in_flight)
+    pipe = codec_mod.FramePipeline(dev, depth, model=net) if depth > 1 else None
+    sc = codec_mod.StreamCodec(net, ctx.q, block_size=512, rank=rank, world=world, coder="bypass")
+
+    def checksum(rec):          # order-independent digest of a reconstruction: (voxels, sum of coordinates, sum of 8-bit colours)
+        r = rec.double()
+        return (int(rec.shape[0]), float(r[:, :3].sum()), float(torch.round(r[:, 3:] * 255).sum()))
+
+    def run(frames_of, keep):
+        return sc.run([(lambda i=i: frames_of(i)) for i in range(n_frames)], sizes=sizes, keep=keep, pipeline=pipe)
+
+    with torch.no_grad():
+        for i in mine[:2]:                                       # warm-up: allocator pools, packed weights, worker streams
+            sc.code_frame(resident[i])
+        if pipe is not None:
+            pipe.map(lambda i: sc.code_frame(resident[i]), mine[:depth])
+        _barrier(ctx)
+        clocks = ClockSampler(range(world)) if rank == 0 else None
+        _barrier(ctx)
+        if clocks is not None:
+            clocks.mark()
+        l0 = pkg._lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = run(lambda i: resident[i], checksum)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_res = e0.elapsed_time(e1)
+        launches = pkg._lib.launch_count() - l0
+        _barrier(ctx)
+        clk = clocks.stop() if clocks is not None else None
+        # end to end: every frame from pinned host memory, reconstruction back to the host
+        pinned_out = {}
+        io = [0, 0]
+
+        def e2e_frame(i):
+            x = host[i].to(dev, non_blocking=True)
+            rec = sc.code_frame(x)
+            buf = pinned_out.get(i)
+            if buf is None or buf.shape != rec.shape:
+                buf = pinned_out[i] = torch.empty(rec.shape, dtype=rec.dtype, pin_memory=True)
+            buf.copy_(rec, non_blocking=True)
+            io[0] += x.numel() * 4
+            io[1] += rec.numel() * rec.element_size()
+            return rec
+        _barrier(ctx)
+        e0.record()
+        if pipe is None:
+            for i in mine:
+                e2e_frame(i)
+        else:
+            pipe.map(e2e_frame, mine)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_e2e = e0.elapsed_time(e1)
+    ms_res_max, ms_e2e_max = _reduce(ctx, ms_res, "MAX"), _reduce(ctx, ms_e2e, "MAX")
+    ms_res_min = -_reduce(ctx, -ms_res, "MAX")
+    h2d, d2h = _reduce(ctx, io[0], "SUM"), _reduce(ctx, io[1], "SUM")
+    launches = _reduce(ctx, launches, "SUM")
+    if pipe is not None:
+        pipe.close()
+    if rank != 0:
+        return
+    total = float(sum(sizes))
+    loads = [sum(sizes[i] for i in codec_mod.my_units(sizes, world, r)) for r in range(world)]
+    line = {"metric": "Mpoints/s encode+decode at 11-bit, 64-frame stream sharded by frame", "value": total / (ms_res_max * 1e3), "unit": UNIT,
+            "n_gpus": world, "steps": 1, "warmup": 2, "ms_per_step": ms_res_max, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
+            "config": {"workload": f"CVPR_inverse_scaling stream11: {n_frames} synthetic 11-bit frames ({int(total)} voxels, 4 generated frames x integer "
+                                   "translations), block_size 512, compress+decompress through codec.StreamCodec, random-init weights, q=(0.5,0.5); "
+                                   "a step = the whole sequence", "sharding": f"{world} rank(s), frames assigned largest-first (LPT), no collective",
+                       "in_flight": depth, "l2": "every frame (40 MB of input, > 1 GB of intermediates) exceeds the 126 MB L2",
+                       "load_imbalance": {"voxels_per_rank": loads, "max_over_mean": max(loads) / (sum(loads) / world),
+                                          "rank_ms_max_over_min": ms_res_max / ms_res_min}},
+            "clocks": clk, "e2e": {"value": total / (ms_e2e_max * 1e3), "unit": UNIT, "ms_per_step": ms_e2e_max, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches),
+            "frames": {str(i): list(res[i]) for i in sorted(res)[:4]}, "frames_coded": len(res),
+            "digest": float(sum(v[1] + v[2] for v in res.values())) if res else None}
+    ctx.emit(line)
+
+
+
+# ----------------------------------------------------------------------------------------- configs[3]: the training step
+def training_batch(seed, n_blocks=8, block=256, min_points=300):
+    """`n_blocks` 256^3 crops of the synthetic 10-bit cloud (configs/CVPR_inverse_scaling_256.yaml: block 256, min_points_train 300;
+    BASELINE.json asks for batch 8 per GPU, the yaml has 4), coordinates local to the crop, one batch index per crop."""
+    import numpy as np
+    pts, rgb = make_frame("frame10", seed=seed)
+    rng = np.random.default_rng(7 + seed)
+    coords, feats = [], []
+    while len(coords) < n_blocks:
+        origin = pts[rng.integers(len(pts))] - rng.integers(32, block - 32, size=3)
+        sel = np.all((pts >= origin) & (pts < origin + block), axis=1)
+        if sel.sum() < min_points:
+            continue
+        b = len(coords)
+        coords.append(np.concatenate([np.full((int(sel.sum()), 1), b, np.int32), (pts[sel] - origin).astype(np.int32)], axis=1))
+        feats.append(rgb[sel].astype(np.float32))
+    return np.concatenate(coords), np.concatenate(feats)
+
+
+def run_train(ctx):
+    """One optimiser step of /root/reference/train.py:195-234 per bench step: forward (train mode, tcgen05 convolutions), the
+    configured losses, backward (input gradients on the inverse kernel maps, weight gradients on the tensor cores), gradient
+    all-reduce over NCCL in buckets launched during backward, clip, both Adam steps.  Weak scaling: 8 blocks per rank."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    args, dev, pkg, net, rank, world = ctx.args, ctx.dev, ctx.pkg, ctx.net, ctx.rank, ctx.world
+    training = importlib.import_module(pkg.__name__ + ".training")
+    loss_mod = importlib.import_module(pkg.__name__ + ".model.loss")
+    c_np, f_np = training_batch(rank)
+    hc, hf = torch.from_numpy(c_np).pin_memory(), torch.from_numpy(f_np).pin_memory()
+    dc, df = hc.to(dev), hf.to(dev)
+    g = torch.Generator().manual_seed(100 + rank)
+    q = torch.rand((8, 2), generator=g).to(dev)
+    n_points = int(c_np.shape[0])
+    n_params = sum(p.numel() for p in net.parameters())
+
+    def time_steps(tr, steps, warmup, e2e=False):
+        for _ in range(warmup):
+            tr.step(dc, df, q)
+        _barrier(ctx)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for _ in range(steps):
+            if e2e:
+                loss, aux, _ = tr.step(hc.to(dev, non_blocking=True), hf.to(dev, non_blocking=True), q)
+                last = float(loss)                                   # device -> host read of the step's result
+            else:
+                loss, aux, _ = tr.step(dc, df, q)
+        e1.record()
+        torch.cuda.synchronize()
+        return _reduce(ctx, e0.elapsed_time(e1), "MAX") / steps, (float(loss) if last is None else last)
+
+    W = max(args.warmup, 3)
+    tr = training.Trainer(net, loss_mod.default_loss_config(), world=world, overlap=True)
+    clocks = ClockSampler(range(world)) if rank == 0 else None
+    ms_warm, _ = time_steps(tr, 1, W)                                 # warm-up (allocator, packed weights, NCCL channels)
+    if clocks is not None:
+        clocks.mark()
+    l0 = pkg._lib.launch_count()
+    ms, loss = time_steps(tr, args.steps, 0)
+    launches = (pkg._lib.launch_count() - l0) // max(args.steps, 1)
+    clk = clocks.stop() if clocks is not None else None
+    ms_e2e, _ = time_steps(tr, args.steps, 1, e2e=True)
+    extra = {}
+    if world > 1:
+        # the same step with ONE flat all-reduce after backward (nothing overlapped), and the all-reduce alone
+        tr_flat = training.Trainer(net, loss_mod.default_loss_config(), world=world, overlap=False)
+        ms_flat, _ = time_steps(tr_flat, args.steps, 2)
+        flat = torch.zeros(sum(p.numel() for p in tr.model_params), device=dev)
+        for _ in range(3):
+            dist.all_reduce(flat)
+        _barrier(ctx)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            dist.all_reduce(flat)
+        e1.record()
+        torch.cuda.synchronize()
+        ar_ms = _reduce(ctx, e0.elapsed_time(e1), "MAX") / 10
+        nbytes = flat.numel() * 4
+        extra = {"allreduce": {"bytes": nbytes, "ms": ar_ms, "algbw_gbs": nbytes / ar_ms / 1e6, "busbw_gbs": nbytes / ar_ms / 1e6 * 2 * (world - 1) / world,
+                               "buckets": len(tr.buckets.buckets)},
+                 "ms_per_step_allreduce_after_backward": ms_flat, "exposed_comm_ms_removed_by_overlap": ms_flat - ms}
+    total_points = _reduce(ctx, n_points, "SUM")
+    if rank != 0:
+        return
+    line = {"metric": "Mpoints/s trained (forward + losses + backward + all-reduce + optimiser step), 256^3 blocks, batch 8 per GPU", "value": total_points / (ms * 1e3),
+            "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W, "ms_per_step": ms, "steps_per_s": 1e3 / ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
+            "config": {"workload": "CVPR_inverse_scaling_256 train256: 8 synthetic 256^3 crops of the 10-bit cloud per rank per step (the yaml's batch_size is 4), "
+                                   f"{n_points} voxels on rank 0, widths 128 / 192, random-init weights, Adam 1e-4 / 1e-3, clip 1.0",
+                       "sharding": f"{world} rank(s), data parallel, bucketed NCCL gradient all-reduce launched during backward", "parameters": n_params,
+                       "l2": "activations of one step (> 2 GB) exceed the 126 MB L2", "conv_mode": args.conv_mode},
+            "clocks": clk, "loss": loss,
+            "e2e": {"value": total_points / (ms_e2e * 1e3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(hc.numel() * 4 + hf.numel() * 4) * world,
+                    "d2h_bytes_per_step": 4 * world},
+            "gpu_launches": int(launches)}
+    line.update(extra)
+    ctx.emit(line)
+
 
 
 if __name__ == "__main__":

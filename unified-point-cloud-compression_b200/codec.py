@@ -43,27 +43,48 @@ def gather_results(local, world, rank, dst=0):
 
 
 class StreamCodec:
-    """Codes the frames of a sequence that fall to this rank.  `net` is a UnifiedModel on this rank's GPU."""
+    """Codes the frames of a sequence that fall to this rank.  `net` is a UnifiedModel on this rank's GPU.
 
-    def __init__(self, net, q, block_size=1024, rank=0, world=1):
+    coder="host": compress + decompress in the component form (model.py:94-250), strings through the host range coder.
+    coder="bypass": the same GPU work per block (`encode_block` / `decode_block`) with the symbols handed from the encoder to the
+    decoder on the device -- the metric's definition (the range coder stays on the host and outside the graft).
+    Blocks follow the reference's partition (model.py:121-127; evaluate.py:39-46: block_size 1024 for 10-bit, 512 for 11-bit)."""
+
+    def __init__(self, net, q, block_size=1024, rank=0, world=1, coder="host"):
+        assert coder in ("host", "bypass")
         self.net, self.q, self.block_size = net, q, block_size
-        self.rank, self.world = rank, world
+        self.rank, self.world, self.coder = rank, world, coder
 
     def code_frame(self, cloud):
-        """compress + decompress one frame (component form, model.py:94-250) -> (N,6) reconstruction."""
+        """compress + decompress one frame -> (N,6) reconstruction."""
         with torch.no_grad():
-            strings, shapes, ks, coords, qs = self.net.compress(cloud, self.q, block_size=self.block_size)
-            return self.net.decompress(coordinates=coords, strings=strings, shape=shapes, k=ks, q_vals=qs)
+            if self.coder == "host":
+                strings, shapes, ks, coords, qs = self.net.compress(cloud, self.q, block_size=self.block_size)
+                return self.net.decompress(coordinates=coords, strings=strings, shape=shapes, k=ks, q_vals=qs)
+            from .model.model import partition_blocks
+            x_sorted, counts = partition_blocks(cloud, self.block_size)
+            pts, feats, start = [], [], 0
+            for count in counts:
+                enc = self.net.encode_block(x_sorted[start:start + count], self.q)
+                ys = enc["y_symbols"]
+                x_hat = self.net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], self.q)
+                pts.append(x_hat.C); feats.append(x_hat.F)
+                start += count
+            return self.net.finalize(torch.cat(pts, 0), torch.cat(feats, 0))
 
-    def run(self, frames, sizes=None, keep=lambda rec: int(rec.shape[0])):
+    def run(self, frames, sizes=None, keep=lambda rec: int(rec.shape[0]), pipeline=None):
         """frames: sequence of (N,6) tensors or zero-argument loaders; sizes: point counts used for the schedule
-        (default: len of each frame).  Returns {frame index: keep(reconstruction)} gathered on rank 0."""
+        (default: len of each frame).  pipeline: a FramePipeline -> this rank's frames are coded `depth` at a time.
+        Returns {frame index: keep(reconstruction)} gathered on rank 0."""
         if sizes is None:
             sizes = [int(f.shape[0]) for f in frames]
-        local = {}
-        for i in my_units(sizes, self.world, self.rank):
-            f = frames[i]() if callable(frames[i]) else frames[i]
-            local[i] = keep(self.code_frame(f))
+        mine = my_units(sizes, self.world, self.rank)
+        load = lambda i: frames[i]() if callable(frames[i]) else frames[i]
+        if pipeline is None:
+            local = {i: keep(self.code_frame(load(i))) for i in mine}
+        else:
+            recs = pipeline.map(lambda i: self.code_frame(load(i)), mine)
+            local = {i: keep(r) for i, r in zip(mine, recs)}
         return gather_results(local, self.world, self.rank)
 
 

@@ -98,16 +98,20 @@ class UnifiedModel(CompressionModel):
         y, k = self.g_a(x)
         enc = self.entropy_model.encode_symbols(y, q)
         enc["k"] = k
+        if getattr(self.g_s, "topk_from_encoder", False):          # measurement switch (bench.py --topk-from encoder)
+            s1 = x.coord_set
+            s2 = s1.strided(2)
+            enc["keep_sets"] = [s2.strided(2), s2, s1]
         return enc
 
-    def decode_block(self, y_points, z_symbols, y_symbol_source, k, q):
+    def decode_block(self, y_points, z_symbols, y_symbol_source, k, q, keep_sets=None):
         """coords down x2 -> entropy decode -> g_s on the GPU; returns the SparseTensor x_hat."""
         y_points = y_points.to(torch.int32)
         y_set = so.coord_set_of(y_points, 8) or ME.SparseTensor(
             torch.empty((y_points.shape[0], 0), device=y_points.device), y_points, tensor_stride=8).coord_set
         z_set = SparseSynthesisTransform.coords_down(y_set, 2)
         y_hat = self.entropy_model.decode_symbols(y_set.coords, z_set.coords, z_symbols, y_symbol_source, q)
-        return self.g_s(y_hat, k=k)
+        return self.g_s(y_hat, k=k, keep_sets=keep_sets)
 
     # -- public API (model.py:94-250) ----------------------------------------------------------------
     def compress(self, pointcloud, q, path=None, block_size=1024, scaling_factor=1.0):

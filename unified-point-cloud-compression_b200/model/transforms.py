@@ -129,15 +129,20 @@ class SparseSynthesisTransform(nn.Module):
         return coord_set
 
     # -- forward -----------------------------------------------------------------------------
-    def forward(self, y, coords=None, k=None):
+    def forward(self, y, coords=None, k=None, keep_sets=None):
+        """keep_sets (measurement only, bench.py --topk-from encoder): the true coordinate sets at strides 4, 2, 1.  The head and
+        the top-k still run, but each level is pruned with the TRUE occupancy -- what a trained model's top-k selects -- so the
+        next level sees the candidate count a deployment sees instead of the scattered set random-init logits keep."""
         x = y
         predictions = []
-        for up, head, k_level in ((self.up_1, self.predict_1, k[0]), (self.up_2, self.predict_2, k[1]),
-                                  (self.up_3, self.predict_3, k[2])):
+        for lvl, (up, head, k_level) in enumerate(((self.up_1, self.predict_1, k[0]), (self.up_2, self.predict_2, k[1]),
+                                                   (self.up_3, self.predict_3, k[2]))):
             x = up(x)
             pred = self._head(head, x)
             predictions.append(pred)
             mask = self._topk_prediction(pred, k_level)
+            if keep_sets is not None:
+                mask = keep_sets[lvl].lookup(x.C) >= 0
             n_avail = [x.F.shape[0]] if len(k_level) == 1 else count_per_batch(x)
             n_keep = sum(min(int(kk), na) for kk, na in zip(k_level, n_avail)) if len(n_avail) == len(k_level) else None
             x = self._prune_tensor(x, mask, n_keep, reorder=head is not self.predict_3)
