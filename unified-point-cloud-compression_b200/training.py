@@ -128,8 +128,9 @@ class Trainer:
         # gradient all-reduce overlapped with backward (hooks); overlap=False keeps the single flat all-reduce after backward
         self.buckets = GradBuckets(self.model_params, world) if (overlap and world > 1) else None
 
-    def step(self, coords, feats, q):
-        """coords (N,4) int (batch,x,y,z), feats (N,3) rgb in [0,1], q (B,2).  Returns (loss, aux_loss, parts)."""
+    def forward_backward(self, coords, feats, q):
+        """Forward, losses, backward and the gradient all-reduce of the model parameters (their .grad then hold the mean over
+        the ranks).  Returns (loss, parts)."""
         self.model.train()
         self.model_optimizer.zero_grad(set_to_none=True)
         self.bottleneck_optimizer.zero_grad(set_to_none=True)
@@ -145,6 +146,11 @@ class Trainer:
         else:
             loss.backward()
             allreduce_mean_(self.model_params, self.world)
+        return loss, parts
+
+    def step(self, coords, feats, q):
+        """coords (N,4) int (batch,x,y,z), feats (N,3) rgb in [0,1], q (B,2).  Returns (loss, aux_loss, parts)."""
+        loss, parts = self.forward_backward(coords, feats, q)
         torch.nn.utils.clip_grad_norm_(self.model.parameters(), self.clip)
         self.model_optimizer.step()
         aux = self.model.aux_loss()
