@@ -617,19 +617,6 @@ static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const in
     PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)wpacked & 15) == 0, "pcg_conv_fwd_tc: operands must be 16-byte aligned");
     if (n_out <= 0) return 0;
     const int cin_p = tc_cin_p(cin), rb = tc_rb(cin_p);
-    PcgEncodeTiled encode = pcg_tensor_map_encoder();
-    PCG_CHECK_ARG(encode != nullptr, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled is not available from this driver");
-    CUtensorMap tm;
-    {
-        cuuint64_t dims[2] = {(cuuint64_t)cin_p, (cuuint64_t)n_in};
-        cuuint64_t strides[1] = {(cuuint64_t)cin_p * 2};
-        cuuint32_t box[2] = {(cuuint32_t)(rb / 2), 1};                  // tile::gather4: one row per index
-        cuuint32_t estr[2] = {1, 1};
-        CUtensorMapSwizzle sw = rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-        CUresult r = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(feats_bf16), dims, strides, box, estr,
-                            CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        PCG_CHECK_ARG(r == CUDA_SUCCESS, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled failed (%d) for n_in=%ld cin_p=%d", (int)r, n_in, cin_p);
-    }
     TcParams p;
     p.nbr = nbr; p.nbr_pitch = nbr_pitch; p.tile_mask = tile_mask;
     p.wpacked = reinterpret_cast<const uint8_t *>(wpacked);
@@ -719,6 +706,20 @@ static int conv_fwd_tc_impl(const void *feats_bf16, long n_in, int cin, const in
 #undef PCG_MT
         PCG_LAUNCHED();
         return 0;
+    }
+    // TMA gather4 arm only: the tensor map of the feature rows (the LSU kernel above never reads one, so it is not encoded there)
+    PcgEncodeTiled encode = pcg_tensor_map_encoder();
+    PCG_CHECK_ARG(encode != nullptr, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled is not available from this driver");
+    CUtensorMap tm;
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)cin_p, (cuuint64_t)n_in};
+        cuuint64_t strides[1] = {(cuuint64_t)cin_p * 2};
+        cuuint32_t box[2] = {(cuuint32_t)(rb / 2), 1};                  // tile::gather4: one row per index
+        cuuint32_t estr[2] = {1, 1};
+        CUtensorMapSwizzle sw = rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+        CUresult r = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(feats_bf16), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        PCG_CHECK_ARG(r == CUDA_SUCCESS, "pcg_conv_fwd_tc: cuTensorMapEncodeTiled failed (%d) for n_in=%ld cin_p=%d", (int)r, n_in, cin_p);
     }
     p.tmem_cols = 32;
     while (p.tmem_cols < p.cout_p) p.tmem_cols <<= 1;
