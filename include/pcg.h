@@ -235,6 +235,10 @@ int pcg_activation(const float *x, long n, int act, float *out, void *stream);
  * beta (C), gamma (C x C) are the re-parametrised values. */
 int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
                 void *stream);
+/* The same layer at the precision of the tensor-core mode: |x| gamma^T as one bf16 product with fp32 accumulation (c = 32, 64, 128),
+ * and optionally (out_bf16 != NULL) the output rows a second time as the bf16 operand image of the next tensor-core layer. */
+int pcg_gdn_fwd_bf16(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out, void *out_bf16,
+                     void *stream);
 
 /* ---- occupancy top-k + prune (transforms.py:228-282, ME.MinkowskiPruning ME5) ---------------
  * mask[i] = 1 for the k rows of batch `batch` with the largest logits (ties: smaller row first);

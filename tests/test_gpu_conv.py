@@ -159,8 +159,16 @@ def test_gdn_matches_reference_expression(pkg, dev):
         norm = torch.nn.functional.conv1d(torch.abs(x.T.unsqueeze(0)), gamma.reshape(c, c, 1), beta)[0].T
         for inverse in (False, True):
             ref = x * norm if inverse else x * (1.0 / norm)
-            out = so.gdn(x.to(dev), beta.to(dev), gamma.to(dev), inverse).cpu()
-            assert rel_l2(out.numpy(), ref.numpy()) < 1e-5
+            for mode, tol in (("f32", 1e-5), ("auto", 3e-3)):       # auto: the norm is one bf16 product (pcg_gdn_fwd_bf16)
+                prev = so.set_conv_mode(mode)
+                try:
+                    o = so.gdn(x.to(dev), beta.to(dev), gamma.to(dev), inverse)
+                finally:
+                    so.set_conv_mode(prev)
+                assert rel_l2(o.cpu().numpy(), ref.numpy()) < tol, (mode, n, c, inverse)
+                shadow = getattr(o, "_pcg_bf16", None)
+                if mode == "auto" and c in (32, 128):                # the bf16 operand image of the next layer comes out of the same kernel
+                    assert shadow is not None and torch.equal(shadow[0], o.to(torch.bfloat16))
 
 
 def test_channelwise_conv_k9(pkg, dev):

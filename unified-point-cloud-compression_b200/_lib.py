@@ -59,6 +59,7 @@ _PROTOS = {
     "pcg_channelwise_conv": (_I, [_P, _I, _P, _L, _I, _L, _P, _I, _P, _P]),
     "pcg_activation": (_I, [_P, _L, _I, _P, _P]),
     "pcg_gdn_fwd": (_I, [_P, _L, _I, _P, _P, _I, _P, _P]),
+    "pcg_gdn_fwd_bf16": (_I, [_P, _L, _I, _P, _P, _I, _P, _P, _P]),
     "pcg_topk_mask": (_I, [_P, _P, _L, _I, _L, _P, _P, _SZ, _P]),
     "pcg_prune_rows": (_I, [_P, _P, _L, _I, _P, _P, _P, _P, _P, _SZ, _P]),
     "pcg_nn_search": (_I, [_P, _P, _L, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P]),

@@ -231,9 +231,12 @@ __device__ __forceinline__ void split_bf16x2(float v0, float v1, uint32_t &hi, u
     lo = *reinterpret_cast<const uint32_t *>(&l);
 }
 
-template <int C>
+// SPLIT = 3: bf16x3 (fp32-grade); SPLIT = 1: the hi x hi product only (bf16-grade norm: the mode whose convolutions run on bf16
+// operands anyway).  out_bf16 (optional): the same rows also as the bf16 operand image of the next tensor-core layer.
+template <int C, int SPLIT>
 __global__ void __launch_bounds__(256) k_gdn_mma16(const float *__restrict__ x, long n, const float *__restrict__ beta,
-                                                   const float *__restrict__ gamma, int inverse, float *__restrict__ out) {
+                                                   const float *__restrict__ gamma, int inverse, float *__restrict__ out,
+                                                   __nv_bfloat16 *__restrict__ out_bf16) {
     constexpr int Q = C / 32, NT = C / 8;
     extern __shared__ uint4 bq_s[];                 // [Q][2][NT][32]: {b0_hi, b1_hi, b0_lo, b1_lo} of output channel nt*8+g
     for (int i = threadIdx.x; i < Q * 2 * NT * 32; i += blockDim.x) {
@@ -273,8 +276,10 @@ __global__ void __launch_bounds__(256) k_gdn_mma16(const float *__restrict__ x, 
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) {
                     const uint4 b = bq[nt * 32];
-                    mma_16816_bf16(acc[nt], al[0], al[1], al[2], al[3], b.x, b.y);
-                    mma_16816_bf16(acc[nt], ah[0], ah[1], ah[2], ah[3], b.z, b.w);
+                    if (SPLIT == 3) {
+                        mma_16816_bf16(acc[nt], al[0], al[1], al[2], al[3], b.x, b.y);
+                        mma_16816_bf16(acc[nt], ah[0], ah[1], ah[2], ah[3], b.z, b.w);
+                    }
                     mma_16816_bf16(acc[nt], ah[0], ah[1], ah[2], ah[3], b.x, b.y);
                 }
             }
@@ -293,17 +298,19 @@ __global__ void __launch_bounds__(256) k_gdn_mma16(const float *__restrict__ x, 
                 o.x = inverse ? xv.x * n0 : xv.x * (1.0f / n0);
                 o.y = inverse ? xv.y * n1 : xv.y * (1.0f / n1);
                 *reinterpret_cast<float2 *>(out + r * C + col) = o;
+                if (out_bf16) *reinterpret_cast<__nv_bfloat162 *>(out_bf16 + r * C + col) = __floats2bfloat162_rn(o.x, o.y);
             }
         }
     }
 }
 
-template <int C>
-static int launch_gdn_mma16(const float *x, long n, const float *beta, const float *gamma, int inverse, float *out, cudaStream_t st) {
+template <int C, int SPLIT>
+static int launch_gdn_mma16(const float *x, long n, const float *beta, const float *gamma, int inverse, float *out, __nv_bfloat16 *out_bf16,
+                            cudaStream_t st) {
     const size_t smem = (size_t)(C / 32) * 2 * (C / 8) * 32 * sizeof(uint4);
-    PCG_CUDA(cudaFuncSetAttribute(k_gdn_mma16<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PCG_CUDA(cudaFuncSetAttribute(k_gdn_mma16<C, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long tiles = cdiv(n, 128);
-    k_gdn_mma16<C><<<(unsigned)(tiles < 2 * PCG_SMS ? tiles : 2 * PCG_SMS), 256, smem, st>>>(x, n, beta, gamma, inverse, out);
+    k_gdn_mma16<C, SPLIT><<<(unsigned)(tiles < 2 * PCG_SMS ? tiles : 2 * PCG_SMS), 256, smem, st>>>(x, n, beta, gamma, inverse, out, out_bf16);
     PCG_LAUNCHED();
     return 0;
 }
@@ -318,6 +325,20 @@ static int launch_gdn_mma(const float *x, long n, const float *beta, const float
     return 0;
 }
 
+// bf16-grade variant for the tensor-core mode: one bf16 product for |x| gamma^T (relative error of the norm ~2^-9, the precision
+// of the convolutions around it) and, optionally, the result also as bf16 operand rows for the next layer (c in 32 / 64 / 128).
+extern "C" int pcg_gdn_fwd_bf16(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
+                                void *out_bf16, void *stream) {
+    if (n <= 0) return 0;
+    cudaStream_t st = as_stream(stream);
+    PCG_CHECK_ARG(c == 128 || c == 64 || c == 32, "pcg_gdn_fwd_bf16: c=%d must be 32, 64 or 128", c);
+    PCG_CHECK_ARG((((uintptr_t)x | (uintptr_t)out) & 15) == 0 && ((uintptr_t)beta & 7) == 0 && ((uintptr_t)out_bf16 & 3) == 0, "pcg_gdn_fwd_bf16: misaligned buffers");
+    __nv_bfloat16 *ob = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
+    if (c == 128) return launch_gdn_mma16<128, 1>(x, n, beta, gamma, inverse, out, ob, st);
+    if (c == 64) return launch_gdn_mma16<64, 1>(x, n, beta, gamma, inverse, out, ob, st);
+    return launch_gdn_mma16<32, 1>(x, n, beta, gamma, inverse, out, ob, st);
+}
+
 extern "C" int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out,
                            void *stream) {
     if (n <= 0) return 0;
@@ -325,9 +346,9 @@ extern "C" int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, con
     const bool aligned = (((uintptr_t)x | (uintptr_t)out) & 15) == 0 && ((uintptr_t)beta & 7) == 0;
     static const bool tf32 = getenv("PCG_GDN") && !strcmp(getenv("PCG_GDN"), "tf32");     // A/B knob: the 3xTF32 version
     if (aligned && !tf32) {
-        if (c == 128) return launch_gdn_mma16<128>(x, n, beta, gamma, inverse, out, st);
-        if (c == 64) return launch_gdn_mma16<64>(x, n, beta, gamma, inverse, out, st);
-        if (c == 32) return launch_gdn_mma16<32>(x, n, beta, gamma, inverse, out, st);
+        if (c == 128) return launch_gdn_mma16<128, 3>(x, n, beta, gamma, inverse, out, nullptr, st);
+        if (c == 64) return launch_gdn_mma16<64, 3>(x, n, beta, gamma, inverse, out, nullptr, st);
+        if (c == 32) return launch_gdn_mma16<32, 3>(x, n, beta, gamma, inverse, out, nullptr, st);
     }
     if (aligned && c == 128) return launch_gdn_mma<128>(x, n, beta, gamma, inverse, out, st);
     if (aligned && c == 64) return launch_gdn_mma<64>(x, n, beta, gamma, inverse, out, st);

@@ -767,9 +767,20 @@ def activation(feats, act):
 
 
 def gdn(feats, beta, gamma, inverse):
+    """x * (beta + |x| gamma^T)^-+1 (model/blocks.py:26-57).  "f32" mode: bf16x3 split products (fp32-grade).  Otherwise the norm
+    is one bf16 product -- the precision of the convolutions on either side -- and the rows are also emitted as the bf16 operand
+    image the next tensor-core layer reads (no separate conversion pass)."""
     f = feats.contiguous()
     out = torch.empty_like(f)
-    call("pcg_gdn_fwd", ptr(f), f.shape[0], f.shape[1], ptr(beta.detach().contiguous()), ptr(gamma.detach().contiguous()),
+    c = f.shape[1]
+    if _conv_mode != "f32" and c in (32, 64, 128) and os.environ.get("PCG_GDN_F32") != "1":
+        ob = torch.empty((f.shape[0], c), dtype=torch.bfloat16, device=f.device) if c == cin_padded(c) else None
+        call("pcg_gdn_fwd_bf16", ptr(f), f.shape[0], c, ptr(beta.detach().contiguous()), ptr(gamma.detach().contiguous()),
+             int(bool(inverse)), ptr(out), ptr(ob), stream())
+        if ob is not None:
+            out._pcg_bf16 = (ob, out._version)
+        return out
+    call("pcg_gdn_fwd", ptr(f), f.shape[0], c, ptr(beta.detach().contiguous()), ptr(gamma.detach().contiguous()),
          int(bool(inverse)), ptr(out), stream())
     return out
 
