@@ -556,7 +556,7 @@ def sparse_conv(feats, in_set, out_set, weight, bias, ksize, transposed, act=ACT
     if narrow:
         fb = to_bf16(feats)
         want_bf16 = out in ("bf16", "both")
-        want_f32 = out != "bf16"
+        want_f32 = out != "bf16" or cout != 16          # the bf16 rows are 16 wide: alone they stand for the output only when cout == 16
         of = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device) if want_f32 else None
         ob = torch.empty((n_out, 16), dtype=torch.bfloat16, device=feats.device) if want_bf16 else None
         if prof is not None:
