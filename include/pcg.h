@@ -122,6 +122,12 @@ int pcg_conv_fwd_f32(const float *feats, long n_in, int cin, const int32_t *nbr,
  * forward convolution of G over the inverse kernel map with W[k]^T and needs no entry point of its own. */
 int pcg_conv_bwd_weight_f32(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
                             int K, long n_out, const float *gout, int cout, float *dweight, void *stream);
+/* The same with the tiles split into parallel slices (scratch of pcg_conv_bwd_weight_f32_scratch_bytes() bytes; partial sums
+ * added in ascending slice order: still one fixed summation order).  Serves the layers the tensor-core kernel does not take. */
+size_t pcg_conv_bwd_weight_f32_scratch_bytes(int K, int cin, int cout, long n_out);
+int pcg_conv_bwd_weight_f32_sliced(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
+                                   int K, long n_out, const float *gout, int cout, void *scratch, size_t scratch_bytes,
+                                   float *dweight, void *stream);
 /* The same gradient on the tensor cores (tcgen05, bf16 operands, fp32 accumulation in TMEM): per offset a GEMM whose reduction
  * dimension is the row index, both operands taken MN-major straight from the gathered row tiles.  feats_bf16: [n_in][roundup64(cin)],
  * gout_bf16: [n_out][roundup64(cout)] (zero padded); 33 <= cin <= 256, cout <= 256, K <= 128, tile_mask required.  Tiles are

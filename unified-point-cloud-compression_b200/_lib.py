@@ -36,6 +36,8 @@ _PROTOS = {
     "pcg_gather_block": (_I, [_P, _P, _L, _I, _P, _P, _P]),
     "pcg_conv_fwd_f32": (_I, [_P, _L, _I, _P, _L, _I, _L, _P, _P, _I, _I, _P, _P]),
     "pcg_conv_bwd_weight_f32": (_I, [_P, _I, _P, _L, _P, _I, _L, _P, _I, _P, _P]),
+    "pcg_conv_bwd_weight_f32_scratch_bytes": (_SZ, [_I, _I, _I, _L]),
+    "pcg_conv_bwd_weight_f32_sliced": (_I, [_P, _I, _P, _L, _P, _I, _L, _P, _I, _P, _SZ, _P, _P]),
     "pcg_conv_bwd_weight_tc_scratch_bytes": (_SZ, [_I, _I, _I, _L]),
     "pcg_conv_bwd_weight_tc": (_I, [_P, _I, _P, _I, _P, _L, _P, _I, _L, _P, _SZ, _P, _P]),
     "pcg_packed_weight_bytes": (_SZ, [_I, _I, _I]),

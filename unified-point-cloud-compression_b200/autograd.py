@@ -63,8 +63,10 @@ class _SparseConv(torch.autograd.Function):
                 call("pcg_conv_bwd_weight_tc", ptr(fb), cin, ptr(gb), cout, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n,
                      ptr(ws), ws.numel(), ptr(dw), stream())
             else:
-                call("pcg_conv_bwd_weight_f32", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n, ptr(g), cout,
-                     ptr(dw), stream())
+                nb = so._lib.load().pcg_conv_bwd_weight_f32_scratch_bytes(K, cin, cout, out_set.n)
+                ws = so.scratch(nb, g.device) if nb else None
+                call("pcg_conv_bwd_weight_f32_sliced", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n, ptr(g), cout,
+                     ptr(ws), nb, ptr(dw), stream())
             g_weight = dw.view_as(weight)
         if has_bias and ctx.needs_input_grad[2]:
             g_bias = g.sum(dim=0, keepdim=True)

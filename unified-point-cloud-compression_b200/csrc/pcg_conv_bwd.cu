@@ -12,15 +12,20 @@
 
 __global__ void __launch_bounds__(256) k_conv_bwd_weight(const float *__restrict__ feats, int cin, const int32_t *__restrict__ nbr,
                                                          long pitch, const uint32_t *__restrict__ tile_mask, long n_out,
-                                                         const float *__restrict__ gout, int cout, float *__restrict__ dw) {
+                                                         const float *__restrict__ gout, int cout, float *__restrict__ dw, int K,
+                                                         long tiles_per_slice) {
     __shared__ float xs[BW_ROWS][BW_CI];
     __shared__ __align__(16) float gs[BW_ROWS][BW_CO];
     __shared__ int idx_s[BW_ROWS];
-    const int k = blockIdx.x, ci0 = blockIdx.y * BW_CI, co0 = blockIdx.z * BW_CO;
+    // blockIdx.x = slice * K + k: a slice is a contiguous range of tiles whose partial block goes to dw + slice * K*cin*cout
+    const int k = blockIdx.x % K, slice = blockIdx.x / K, ci0 = blockIdx.y * BW_CI, co0 = blockIdx.z * BW_CO;
+    dw += (size_t)slice * K * cin * cout;
     const int tid = threadIdx.x, ci = tid >> 4, cq = (tid & 15) * 4;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    const long tiles = (n_out + BW_ROWS - 1) / BW_ROWS;
-    for (long t = 0; t < tiles; ++t) {
+    const long tiles_all = (n_out + BW_ROWS - 1) / BW_ROWS;
+    const long t_begin = (long)slice * tiles_per_slice;
+    const long tiles = t_begin + tiles_per_slice < tiles_all ? t_begin + tiles_per_slice : tiles_all;
+    for (long t = t_begin; t < tiles; ++t) {
         if (tile_mask && !((__ldg(tile_mask + t * 4 + (k >> 5)) >> (k & 31)) & 1u)) continue;     // uniform
         const long o0 = t * BW_ROWS;
         if (tid < BW_ROWS) idx_s[tid] = (o0 + tid < n_out) ? __ldg(nbr + (long)k * pitch + o0 + tid) : -1;
@@ -50,14 +55,51 @@ __global__ void __launch_bounds__(256) k_conv_bwd_weight(const float *__restrict
             if (co0 + cq + j < cout) dw[((long)k * cin + ci0 + ci) * cout + co0 + cq + j] = acc[j];
 }
 
-extern "C" int pcg_conv_bwd_weight_f32(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
-                                       int K, long n_out, const float *gout, int cout, float *dweight, void *stream) {
+static long bwf_slices(int K, int cin, int cout, long tiles) {
+    const long ctas = (long)K * cdiv(cin, BW_CI) * cdiv(cout, BW_CO);
+    long s = cdiv(4L * PCG_SMS, ctas);        // small (K, cin, cout) blocks (the narrow head layers) would leave most SMs idle
+    if (s > tiles) s = tiles;
+    if (s > 256) s = 256;
+    return s < 1 ? 1 : s;
+}
+
+extern "C" size_t pcg_conv_bwd_weight_f32_scratch_bytes(int K, int cin, int cout, long n_out) {
+    const long tiles = cdiv(n_out > 0 ? n_out : 1, BW_ROWS);
+    const long s = bwf_slices(K, cin, cout, tiles);
+    return s > 1 ? (size_t)s * K * cin * cout * sizeof(float) + 256 : 0;
+}
+
+__global__ void k_bwd_reduce_partials(const float *__restrict__ partial, int slices, long n, float *__restrict__ dw);
+
+// scratch (optional): with pcg_conv_bwd_weight_f32_scratch_bytes() bytes the tiles are split into slices that run in parallel and
+// whose partial sums are added in ascending order afterwards; without it one CTA per (k, channel block) walks every tile.
+extern "C" int pcg_conv_bwd_weight_f32_sliced(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
+                                              int K, long n_out, const float *gout, int cout, void *scratch, size_t scratch_bytes,
+                                              float *dweight, void *stream) {
     PCG_CHECK_ARG(K >= 1 && K <= 65535 && cin >= 1 && cout >= 1, "pcg_conv_bwd_weight_f32: K=%d cin=%d cout=%d", K, cin, cout);
     PCG_CHECK_ARG(tile_mask == nullptr || K <= 128, "pcg_conv_bwd_weight_f32: tile_mask needs K <= 128");
-    dim3 grid((unsigned)K, (unsigned)cdiv(cin, BW_CI), (unsigned)cdiv(cout, BW_CO));
-    k_conv_bwd_weight<<<grid, 256, 0, as_stream(stream)>>>(feats, cin, nbr, nbr_pitch, tile_mask, n_out, gout, cout, dweight);
+    cudaStream_t st = as_stream(stream);
+    const long tiles = cdiv(n_out > 0 ? n_out : 1, BW_ROWS);
+    long slices = bwf_slices(K, cin, cout, tiles);
+    const long n_w = (long)K * cin * cout;
+    if (slices > 1 && (!scratch || scratch_bytes < (size_t)slices * n_w * sizeof(float))) slices = 1;
+    const long tps = cdiv(tiles, slices);
+    float *dst = slices > 1 ? reinterpret_cast<float *>(scratch) : dweight;
+    dim3 grid((unsigned)(K * slices), (unsigned)cdiv(cin, BW_CI), (unsigned)cdiv(cout, BW_CO));
+    k_conv_bwd_weight<<<grid, 256, 0, st>>>(feats, cin, nbr, nbr_pitch, tile_mask, n_out, gout, cout, dst, K, tps);
     PCG_LAUNCHED();
+    if (slices > 1) {
+        long blocks = cdiv(n_w, 256);
+        if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+        k_bwd_reduce_partials<<<(unsigned)blocks, 256, 0, st>>>(dst, (int)slices, n_w, dweight);
+        PCG_LAUNCHED();
+    }
     return 0;
+}
+
+extern "C" int pcg_conv_bwd_weight_f32(const float *feats, int cin, const int32_t *nbr, long nbr_pitch, const uint32_t *tile_mask,
+                                       int K, long n_out, const float *gout, int cout, float *dweight, void *stream) {
+    return pcg_conv_bwd_weight_f32_sliced(feats, cin, nbr, nbr_pitch, tile_mask, K, n_out, gout, cout, nullptr, 0, dweight, stream);
 }
 
 // ---------------------------------------------------------------------------- weight gradient on the tensor cores
