@@ -130,7 +130,7 @@ int pcg_conv_bwd_weight_f32_sliced(const float *feats, int cin, const int32_t *n
                                    float *dweight, void *stream);
 /* The same gradient on the tensor cores (tcgen05, bf16 operands, fp32 accumulation in TMEM): per offset a GEMM whose reduction
  * dimension is the row index, both operands taken MN-major straight from the gathered row tiles.  feats_bf16: [n_in][roundup64(cin)],
- * gout_bf16: [n_out][roundup64(cout)] (zero padded); 33 <= cin <= 256, cout <= 256, K <= 128, tile_mask required.  Tiles are
+ * gout_bf16: [n_out][roundup64(cout)] (both zero padded); cin <= 256, cout <= 256, K <= 128, tile_mask required.  Tiles are
  * split into slices whose partial sums (scratch) are added in ascending order: deterministic.  dweight: fp32 [K][cin][cout]. */
 size_t pcg_conv_bwd_weight_tc_scratch_bytes(int K, int cin, int cout, long n_out);
 int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const void *gout_bf16, int cout, const int32_t *nbr, long nbr_pitch,

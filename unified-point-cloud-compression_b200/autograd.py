@@ -17,8 +17,18 @@ from ._lib import call, ptr, stream
 
 def bwd_weight_tc_eligible(K, cin, cout):
     """Static rule for the tensor-core weight gradient (pcg_conv_bwd_weight_tc): every layer of the model at its configured widths
-    except the 4-channel input layer, the narrow occupancy-head layers and the 1x1 colour head, which keep the fp32 kernel."""
-    return so.get_conv_mode() != "f32" and K <= 128 and 33 <= cin <= 256 and 16 <= cout <= 256 and ((cin + 127) // 128) * ((cout + 15) // 16 * 16) <= 512
+    -- the narrow occupancy-head layers with their rows padded to 64 channels -- except the 4-channel input layer, which keeps the
+    (sliced) fp32 kernel."""
+    return so.get_conv_mode() != "f32" and K <= 128 and 16 <= cin <= 256 and 1 <= cout <= 256 and ((cin + 127) // 128) * ((cout + 15) // 16 * 16) <= 512
+
+
+def _bf16_rows64(t):
+    """fp32 (n, c) -> bf16 (n, roundup64(c)), zero padded: operand rows of the weight-gradient kernel."""
+    c = t.shape[1]
+    cp = (c + 63) // 64 * 64
+    out = torch.empty((t.shape[0], cp), dtype=torch.bfloat16, device=t.device)
+    call("pcg_f32_to_bf16_rows", ptr(t.contiguous()), t.shape[0], c, cp, ptr(out), stream())
+    return out
 
 
 def _act_grad(gout, out, act):
@@ -54,10 +64,8 @@ class _SparseConv(torch.autograd.Function):
             dw = torch.empty_like(w3)
             if bwd_weight_tc_eligible(K, cin, cout) and tmask is not None and out_set.n > 0 and feats.shape[0] > 0:
                 # tensor cores: bf16 operand rows of F (cached shadow of the forward pass when there is one) and of G
-                fb = so.to_bf16(feats)
-                cp = (cout + 63) // 64 * 64
-                gb = torch.empty((g.shape[0], cp), dtype=torch.bfloat16, device=g.device)
-                call("pcg_f32_to_bf16_rows", ptr(g), g.shape[0], cout, cp, ptr(gb), stream())
+                fb = so.to_bf16(feats) if cin >= 33 else _bf16_rows64(feats)
+                gb = _bf16_rows64(g)
                 lib = so._lib.load()
                 ws = so.scratch(lib.pcg_conv_bwd_weight_tc_scratch_bytes(K, cin, cout, out_set.n), g.device)
                 call("pcg_conv_bwd_weight_tc", ptr(fb), cin, ptr(gb), cout, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n,

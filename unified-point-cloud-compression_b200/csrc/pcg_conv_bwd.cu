@@ -304,7 +304,7 @@ extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const voi
                                       const uint32_t *tile_mask, int K, long n_out, void *scratch, size_t scratch_bytes, float *dweight,
                                       void *stream) {
     PCG_CHECK_ARG(K >= 1 && K <= 128, "pcg_conv_bwd_weight_tc: K=%d must be in [1,128] (tile mask)", K);
-    PCG_CHECK_ARG(cin >= 33 && cin <= 256 && cout >= 1 && cout <= 256, "pcg_conv_bwd_weight_tc: cin=%d (33..256) cout=%d (1..256)", cin, cout);
+    PCG_CHECK_ARG(cin >= 1 && cin <= 256 && cout >= 1 && cout <= 256, "pcg_conv_bwd_weight_tc: cin=%d (1..256) cout=%d (1..256)", cin, cout);
     PCG_CHECK_ARG(tile_mask != nullptr && (nbr_pitch & 127) == 0 && nbr_pitch >= n_out, "pcg_conv_bwd_weight_tc: tile_mask / padded neighbour table required");
     PCG_CHECK_ARG(((uintptr_t)feats_bf16 & 15) == 0 && ((uintptr_t)gout_bf16 & 15) == 0, "pcg_conv_bwd_weight_tc: operands must be 16-byte aligned");
     cudaStream_t st = as_stream(stream);
