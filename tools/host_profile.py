@@ -22,7 +22,7 @@ torch.manual_seed(0)
 net = model_mod.UnifiedModel(bench.model_config()).to(dev).eval()
 net.update()
 q = torch.tensor([[0.5, 0.5]], device=dev)
-pts, rgb = bench.make_frame("frame10", 0)
+pts, rgb = bench.make_frame(sys.argv[1] if len(sys.argv) > 1 else "frame10", 0)
 cloud = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1)).to(dev)
 
 
