@@ -309,3 +309,28 @@ def test_profiler_spans_cover_hash_map_and_entropy_calls(pkg, dev):
         assert d["launches"] >= 1 and d["ms"] > 0 and d["bytes"] > 0, kind
         if not kind.startswith("conv") and kind not in ("gemm_first", "gent_reduce", "head_gather"):
             assert d["flops"] == 0, kind
+
+
+@pytest.mark.parametrize("mode", ["f32", "auto"])
+def test_trained_codec_matches_fp32_oracle(pkg, dev, mode):
+    """The parity gate of the TIMED (bf16 tensor-core) mode on weights whose occupancy logits are separated by TRAINING, not by
+    scaling (tests/golden/trained_w32.npz: the reference's own training step over the CPU oracle, oracle/train_fixture.py):
+    the GPU decode must reproduce the fp32 oracle's decode of the same input almost voxel for voxel, the quantised symbols must
+    agree on >= 99.5 % of the elements, and D1-PSNR / Y-PSNR against the source must agree within 0.05 dB -- on an UNSEEN cloud."""
+    import os
+    from oracle import metric_ref, synth
+    from tests.helpers import GOLDEN
+    if not os.path.exists(os.path.join(GOLDEN, "trained_w32.npz")):
+        pytest.skip("trained fixture missing")
+    z, sd = load_golden("trained_w32")
+    cloud = synth.small_cloud(seed=77, radius=12.0, centre=(26, 26, 26), n_samples=14000)
+    stats = tiny_codec_roundtrip(pkg, dev, width=int(z["width"]), mode=mode, state_dict=sd, cloud=cloud, return_clouds=True,
+                                 min_overlap=0.99, max_symbol_mismatch=0.005)
+    src, rec, rrec = stats["source"], stats["rec"], stats["ref_rec"]
+    got = metric_ref.pointcloud_metrics(src, rec, resolution=63)
+    ref = metric_ref.pointcloud_metrics(src, rrec, resolution=63)
+    ia, _ = align_rows(rrec[:, :3], src[:, :3])
+    print(f"[trained {mode}] voxels {stats['n']}, GPU/oracle decode overlap {stats['overlap']:.4f}, symbol mismatch {stats['symbol_mismatch']:.5f}, "
+          f"oracle decode on source {len(ia) / len(src):.3f}, D1 {got['sym_psnr_mse']:.3f} vs {ref['sym_psnr_mse']:.3f} dB, "
+          f"Y {got['sym_y_psnr']:.3f} vs {ref['sym_y_psnr']:.3f} dB")
+    assert abs(got["sym_psnr_mse"] - ref["sym_psnr_mse"]) <= 0.05 and abs(got["sym_y_psnr"] - ref["sym_y_psnr"]) <= 0.05
