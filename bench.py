@@ -325,6 +325,7 @@ def main():
         so.profiler = so.ConvProfiler()
         step_resident()
         prof = so.profiler.summary()
+        impl_bytes = dict(so.profiler.impl_bytes)
         so.profiler = None
 
     def reduce_max(ms):
@@ -368,29 +369,40 @@ def main():
                 for k, v in sorted(d.items(), key=lambda kv: -kv[1][1])}
 
     def hbm(kind):
+        """CUDA-event time of a kernel group and, where the group has a defined input and output, its ALGORITHMIC bytes
+        (inputs read once + outputs written once; no intermediates, no neighbour tables) as GB/s."""
         d = prof.get(kind, zero)
-        gbs = d["bytes"] / (d["ms"] * 1e-3) / 1e9 if d["ms"] > 0 else 0.0
-        return {"launches": d["launches"], "ms": round(d["ms"], 3), "algorithmic_gb": round(d["bytes"] / 1e9, 3), "achieved_gbs": round(gbs, 1),
-                "frac_of_hbm_peak": round(gbs / pk["hbm_gbs"], 4),
-                "ms_by_shape": {"x".join(map(str, k)): round(v[1], 3) for k, v in sorted(d["by_shape"].items(), key=lambda kv: -kv[1][1])}}
+        out = {"launches": d["launches"], "ms": round(d["ms"], 3),
+               "ms_by_shape": {"x".join(map(str, k)): round(v[1], 3) for k, v in sorted(d["by_shape"].items(), key=lambda kv: -kv[1][1])}}
+        if d["bytes"] > 0 and d["ms"] > 0:
+            gbs = d["bytes"] / (d["ms"] * 1e-3) / 1e9
+            out.update(algorithmic_gb=round(d["bytes"] / 1e9, 3), achieved_gbs=round(gbs, 1), frac_of_hbm_peak=round(gbs / pk["hbm_gbs"], 4))
+        return out
 
-    traffic = None                      # DRAM bytes of the same launches from the committed ncu --set full capture
-    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tp) and args.workload == "frame10":
-        traffic = json.load(open(tp))["tcgen05_conv_dram_bytes_per_step"]
+    # DRAM traffic of the same launches: written by tools/traffic_from_ncu.py from an `ncu --set full` capture of THIS command
+    # (profiles/r02_traffic.json names the capture); null when no capture of this workload is committed
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if os.path.exists(tp) and args.workload == "frame10" and args.topk_from == "decoder":
+        tj = json.load(open(tp))
+        traffic, traffic_src = tj.get("tcgen05_conv_dram_bytes_per_step"), tj.get("source")
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_mt / k_conv_tc + k_gemm_first (tcgen05 sparse conv kernels, all launches of one step)",
                 "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s", "frac": achieved / bf16_peak,
                 "peak_kind": peak_kind, "frac_of_burst_peak": achieved / pk["bf16_burst"], "frac_of_sustained_peak": achieved / pk["bf16_sustained"],
-                "traffic": traffic, "traffic_unit": "DRAM bytes per step over the same launches (ncu --set full; source named in profiles/r01_traffic.json)",
+                "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
                 "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * depth / ms_res if ms_res else None,
                 "per": "one frame (the roofline pass codes a single frame on one stream)",
                 "algorithmic_gflop_per_step": tc_flops / 1e9,
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},
-                "hbm_bound_kernels": {"gent_reduce (k_cells_reduce)": hbm("gent_reduce"), "conv_narrow (occupancy-head layers, k_conv_tc_mt<1, 32|64|128>)": hbm("conv_narrow"),
-                                      "gemm_first (k_gemm_first, T write)": hbm("gemm_first"),
-                                      "head_gather (k_gather_sum: second head layer, GEMM-first)": hbm("head_gather"),
-                                      # north-star pieces 1 and 5: coordinate hash, kernel maps, compaction, entropy model (CUDA events per C-ABI call)
+                "intermediate_bytes_not_counted": {k: int(v) for k, v in impl_bytes.items()},
+                "hbm_bound_kernels": {"gen_transpose (k_gemm_first + k_cells_reduce: parent rows in, child rows out)": hbm("gen_transpose"),
+                                      "  of which k_gemm_first": hbm("gemm_first"), "  of which k_cells_reduce": hbm("gent_reduce"),
+                                      "occupancy_head (first layer on tcgen05 + k_gather_sum: rows in, logits out)": hbm("occupancy_head"),
+                                      "  of which k_gather_sum": hbm("head_gather"),
+                                      "conv_narrow (unfused narrow head layers)": hbm("conv_narrow"),
+                                      # north-star pieces 1 and 5: coordinate hash, kernel maps, compaction, entropy model (CUDA events per C-ABI call;
+                                      # a kernel map's own product is its neighbour table, counted for that call only)
                                       "hash_build (k_hash_insert)": hbm("hash_build"),
                                       "stride_coords (k_insert_strided + compaction)": hbm("stride_coords"),
                                       "generate_coords (k_insert_generated + compaction)": hbm("generate_coords"),
