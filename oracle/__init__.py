@@ -16,4 +16,18 @@ Gaussian likelihood, ``scipy.special.expit`` chains for the factorised prior, an
 ``scipy.spatial.cKDTree`` for the PSNR metric; and ``tests/golden/*.npz`` hold outputs of
 the reference's *own* ``model/*.py`` executed (unmodified, from /root/reference) on top of
 this oracle via ``oracle/shim.py`` (generator: ``oracle/make_golden.py``).
+
+ME conventions that stay UNVERIFIABLE here, and why none of them is observable through the reference's call sites:
+  * which duplicate the default RANDOM_SUBSAMPLE quantisation keeps (we keep the first row): the reference de-duplicates with
+    `sparse_quantize` before every SparseTensor it builds from data (model/model.py:152-161, train.py:204-211), and every other
+    constructor call passes coordinates that are unique by construction;
+  * the row order of strided / generated coordinate sets (ours: first occurrence; ME: hash-map iteration order): every consumer
+    is row-order invariant -- convolutions, pruning by coordinate key (transforms.py:257-282), `features_at_coordinates`, and the
+    bitstream order is re-derived by `sort_tensor` / `sort_points` (utils.py:142-187) on both sides of the channel;
+  * the trilinear corner rule of `features_at_coordinates` off the grid: all call sites query on-grid points
+    (entropy_models.py:294,381,446; loss.py:105,254-271), where interpolation is an exact row lookup;
+  * the kernel-offset enumeration order (ix fastest) and the even-kernel offset range {0..k-1}: they fix which slice of `kernel`
+    multiplies which neighbour, i.e. the meaning of a checkpoint.  Pinned against dense conv3d / conv_transpose3d under the
+    stated weight-index mapping (tests/test_oracle_dense.py); a real-ME checkpoint would be the only further evidence, and the
+    reference ships none (README.md:122).
 """
