@@ -502,6 +502,7 @@ def run_stream(ctx):
             sc.code_frame(resident[i])
         if pipe is not None:
             pipe.map(lambda i: sc.code_frame(resident[i]), mine[:depth])
+        codec_mod.gather_results({-1 - rank: (0, 0.0, 0.0)}, world, rank)      # warm-up of the result gather (first object collective: ~1 s of set-up)
         _barrier(ctx)
         clocks = ClockSampler(range(world)) if rank == 0 else None
         _barrier(ctx)
