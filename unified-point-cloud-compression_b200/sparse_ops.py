@@ -36,7 +36,7 @@ _scratch = {}
 
 def scratch(nbytes, device):
     """Per-device growable workspace (stream-ordered reuse on the current stream)."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _lib.raw_stream())
     buf = _scratch.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=device)
@@ -54,7 +54,7 @@ def ctl(device):
     """Per-(device, stream) int32 control words, zero-initialised once: [0] = sticky status of pcg_hash_build (the one table
     builder without a size read-back of its own), [1:] = counters / status words of the call in flight.  Every C-ABI call
     that takes a counter clears it itself, and every reader synchronises right after its call, so the words are reused."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _lib.raw_stream())
     buf = _ctl.get(key)
     if buf is None:
         buf = _ctl[key] = torch.zeros(8, dtype=torch.int32, device=device)
