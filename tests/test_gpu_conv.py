@@ -385,7 +385,8 @@ def test_conv_transpose_onto_given_coordinates_matches_oracle(pkg, dev, cin, cou
 @pytest.mark.parametrize("cin,cout,ksize,stride,transposed", [(128, 128, 3, 1, False), (128, 128, 5, 2, False), (192, 256, 3, 1, False),
                                                               (192, 192, 2, 2, True), (128, 32, 5, 2, True), (64, 16, 3, 1, False),
                                                               (128, 64, 3, 1, False), (40, 48, 3, 1, False), (128, 192, 3, 1, False),
-                                                              (64, 1, 3, 1, False), (32, 16, 3, 1, False), (16, 1, 3, 1, False)])
+                                                              (64, 1, 3, 1, False), (32, 16, 3, 1, False), (16, 1, 3, 1, False),
+                                                              (4, 128, 5, 2, False), (32, 3, 1, 1, False)])
 def test_weight_gradient_on_tensor_cores(pkg, dev, cin, cout, ksize, stride, transposed):
     """pcg_conv_bwd_weight_tc (tcgen05, MN-major operands taken from the gathered row tiles, sliced + fixed-order reduction):
     bit-exact against the fp32 kernel on integer-valued operands (pins the MN-major descriptors / swizzle / TMEM lane mapping),

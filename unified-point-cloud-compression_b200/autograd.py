@@ -17,9 +17,10 @@ from ._lib import call, ptr, stream
 
 def bwd_weight_tc_eligible(K, cin, cout):
     """Static rule for the tensor-core weight gradient (pcg_conv_bwd_weight_tc): every layer of the model at its configured widths
-    -- the narrow occupancy-head layers with their rows padded to 64 channels -- except the 4-channel input layer, which keeps the
-    (sliced) fp32 kernel."""
-    return so.get_conv_mode() != "f32" and K <= 128 and 16 <= cin <= 256 and 1 <= cout <= 256 and ((cin + 127) // 128) * ((cout + 15) // 16 * 16) <= 512
+    -- the narrow occupancy-head layers and the 4-channel input layer with their rows padded to 64 channels (the fp32 kernel ran
+    the input layer's 125 x 4 x 128 gradient in 18 ms on FFMA; padded 16x it is still a ~2 ms tensor-core job); the fp32 kernel
+    remains the parity mode and serves the 1x1 colour head's K = 1 only through the same rule."""
+    return so.get_conv_mode() != "f32" and K <= 128 and 1 <= cin <= 256 and 1 <= cout <= 256 and ((cin + 127) // 128) * ((cout + 15) // 16 * 16) <= 512
 
 
 def _bf16_rows64(t):
