@@ -1,7 +1,8 @@
 """Train a small codec with the reference's OWN training step and write its weights as a test fixture.
 TEST INFRASTRUCTURE; build container only (needs /root/reference):
 
-    python -m oracle.train_fixture [steps]        ->  tests/golden/trained_w32.npz
+    python -m oracle.train_fixture [steps] [--resume]       ->  tests/golden/trained_w32.npz
+(the committed fixture: 700 steps at 1e-3, then `1400 --resume` at 5e-4)
 
 Why: with random-init weights the occupancy logits are barely separated, so bf16 tensor-core rounding legitimately flips top-k
 membership and the end-to-end parity gates of the timed (bf16) mode can only be loose.  A TRAINED model separates occupied from
@@ -43,11 +44,16 @@ def batch(step, n_clouds=2):
     return torch.cat(coords), torch.cat(feats)
 
 
-def main(steps=400, width=32, lr=1e-3):
+def main(steps=400, width=32, lr=1e-3, resume=False):
     assert shim.available(), "needs /root/reference"
     cfg_all = yaml.safe_load(open(os.path.join(shim.REFERENCE, "configs", "CVPR_inverse_scaling.yaml")))
     cfg = small_config("CVPR_inverse_scaling", width=width)
     net = shim.reference_model(cfg, seed=0)
+    done = 0
+    if resume and os.path.exists(OUT):          # continue from the committed fixture (fresh optimiser state)
+        z = np.load(OUT)
+        net.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/") and not k.split(".")[-1].startswith("_")}, strict=False)
+        done = int(z["steps"])
     import MinkowskiEngine as ME          # the oracle, through the shim
     import loss as ref_loss               # /root/reference/loss.py
     from data.q_func import Q_Func        # /root/reference/data/q_func.py
@@ -65,7 +71,7 @@ def main(steps=400, width=32, lr=1e-3):
     # hundred steps teach no geometry at all (measured: 1.3 % of the decoded voxels on the source after 400 steps)
     q_func = Q_Func(dict(cfg_all["q_map"], lambda_A_max=200, lambda_G_min=50))
     t0 = time.time()
-    for step in range(steps):
+    for step in range(done, done + steps):
         opt.zero_grad()
         opt_b.zero_grad()
         coords, feats = batch(step)
@@ -92,7 +98,7 @@ def main(steps=400, width=32, lr=1e-3):
         aux.backward()
         opt_b.step()
         sched.step()
-        if step % 20 == 0 or step == steps - 1:
+        if step % 20 == 0 or step == done + steps - 1:
             print(f"step {step:4d} loss {float(loss):10.3f} " + " ".join(f"{k}={float(v):.4f}" for k, v in parts.items()) +
                   f" aux {float(aux):.2f} q=({float(q[0, 0]):.2f},{float(q[0, 1]):.2f}) {time.time() - t0:.0f}s", flush=True)
     net.eval()
@@ -107,9 +113,9 @@ def main(steps=400, width=32, lr=1e-3):
     src = {tuple(p) for p in pts.tolist()}
     hit = sum(tuple(int(v) for v in r[:3]) in src for r in rec)
     print(f"decoded voxels on the source: {hit}/{len(pts)} = {hit / len(pts):.3f}", flush=True)
-    np.savez_compressed(OUT, cfg_name="CVPR_inverse_scaling", width=width, steps=steps, **{"sd/" + k: v for k, v in sd.items()})
+    np.savez_compressed(OUT, cfg_name="CVPR_inverse_scaling", width=width, steps=done + steps, **{"sd/" + k: v for k, v in sd.items()})
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 
 
 if __name__ == "__main__":
-    main(int(sys.argv[1]) if len(sys.argv) > 1 else 400)
+    main(int(sys.argv[1]) if len(sys.argv) > 1 else 400, resume="--resume" in sys.argv, lr=5e-4 if "--resume" in sys.argv else 1e-3)
