@@ -50,10 +50,12 @@ class StreamCodec:
     decoder on the device -- the metric's definition (the range coder stays on the host and outside the graft).
     Blocks follow the reference's partition (model.py:121-127; evaluate.py:39-46: block_size 1024 for 10-bit, 512 for 11-bit)."""
 
-    def __init__(self, net, q, block_size=1024, rank=0, world=1, coder="host"):
+    def __init__(self, net, q, block_size=1024, rank=0, world=1, coder="host", batched=False):
+        """batched (bypass coder): the blocks of a frame are coded as ONE batched sparse tensor (block = batch item) instead of
+        one after the other -- same per-block results, one set of launches per frame instead of one per block."""
         assert coder in ("host", "bypass")
         self.net, self.q, self.block_size = net, q, block_size
-        self.rank, self.world, self.coder = rank, world, coder
+        self.rank, self.world, self.coder, self.batched = rank, world, coder, batched
 
     def code_frame(self, cloud):
         """compress + decompress one frame -> (N,6) reconstruction."""
@@ -63,6 +65,11 @@ class StreamCodec:
                 return self.net.decompress(coordinates=coords, strings=strings, shape=shapes, k=ks, q_vals=qs)
             from .model.model import partition_blocks
             x_sorted, counts = partition_blocks(cloud, self.block_size)
+            if self.batched and len(counts) > 1:
+                enc = self.net.encode_blocks(x_sorted, counts, self.q)
+                ys = enc["y_symbols"]
+                x_hat = self.net.decode_block(enc["y_points"], enc["z_symbols"], lambda idx: ys, enc["k"], enc["q"])
+                return self.net.finalize(x_hat.C, x_hat.F)
             pts, feats, start = [], [], 0
             for count in counts:
                 enc = self.net.encode_block(x_sorted[start:start + count], self.q)

@@ -92,6 +92,33 @@ class UnifiedModel(CompressionModel):
         cs.single_batch = True                                     # one block = one batch item: level sizes are row counts
         return ME.SparseTensor(feats, _coord_set=cs)
 
+    def blocks_tensor(self, x_sorted, counts):
+        """All blocks of a frame as ONE batched SparseTensor: block i = batch item i (rows of `x_sorted` grouped by block,
+        `counts[i]` rows each, model.py:121-137).  The reference codes the blocks one after the other, each as its own batch-0
+        tensor; nothing in the codec crosses batch items (kernel maps, per-batch top-k, per-batch gains), so one batched pass
+        computes every block's result with one set of launches instead of one per block."""
+        dev = x_sorted.device
+        batch = torch.repeat_interleave(torch.arange(len(counts), dtype=torch.int32, device=dev),
+                                        torch.as_tensor(counts, device=dev))
+        coords0, _ = so.gather_block(x_sorted)
+        order = so.sort_rows_i32(coords0, morton=True, bits=so.LOCALITY_BITS)      # blocks are disjoint cubes: global Z-order keeps them apart
+        coords4, feats = so.gather_block(x_sorted, order)
+        coords4[:, 0] = batch[order.long()]
+        uniq, index, table = so.unique_first(coords4)
+        if uniq.shape[0] != coords4.shape[0]:
+            coords4, feats = uniq, feats[index.long()]
+        return ME.SparseTensor(feats, _coord_set=so.CoordSet(coords4, 1, table=table))
+
+    def encode_blocks(self, x_sorted, counts, q):
+        """`encode_block` for all blocks of a frame at once (batched); q: (1,2) or (len(counts),2)."""
+        x = self.blocks_tensor(x_sorted, counts)
+        y, k = self.g_a(x)
+        qb = q if q.shape[0] == len(counts) else q.expand(len(counts), 2)
+        enc = self.entropy_model.encode_symbols(y, qb)
+        enc["k"] = k
+        enc["q"] = qb
+        return enc
+
     def encode_block(self, x_block, q):
         """g_a + hyper-analysis + quantisation + CDF indexes on the GPU; returns device symbol buffers + k."""
         x = self.block_tensor(x_block)
