@@ -150,6 +150,8 @@ def main():
                     help="frame10: BASELINE configs[1] (default, the metric's config); block128: configs[0]; stream11: configs[2], 64-frame 11-bit "
                          "stream sharded by frame (strong scaling); train256: configs[3], the training step on 256^3 blocks, batch 8 per GPU")
     ap.add_argument("--frames", type=int, default=64, help="stream11: frames in the sequence")
+    ap.add_argument("--serial-blocks", action="store_true", help="stream11: code the blocks of a frame one after the other (the reference's "
+                    "loop, model.py:137-176) instead of as one batched sparse tensor")
     ap.add_argument("--topk-from", default="decoder", choices=["decoder", "encoder"],
                     help="encoder: prune every decoder level with the TRUE occupancy (what a trained model's top-k selects) instead of the "
                          "random-init logits, which keep a scattered set and make levels 2/3 ~1.5x heavier than any deployment sees")
@@ -495,7 +497,7 @@ def run_stream(ctx):
     resident = {i: h.to(dev) for i, h in host.items()}
     depth = max(1, args.in_flight)
     pipe = codec_mod.FramePipeline(dev, depth, model=net) if depth > 1 else None
-    sc = codec_mod.StreamCodec(net, ctx.q, block_size=512, rank=rank, world=world, coder="bypass")
+    sc = codec_mod.StreamCodec(net, ctx.q, block_size=512, rank=rank, world=world, coder="bypass", batched=not args.serial_blocks)
 
     def checksum(rec):          # order-independent digest of a reconstruction: (voxels, sum of coordinates, sum of 8-bit colours)
         r = rec.double()
@@ -563,7 +565,7 @@ def run_stream(ctx):
             "n_gpus": world, "steps": 1, "warmup": 2, "ms_per_step": ms_res_max, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
             "config": {"workload": f"CVPR_inverse_scaling stream11: {n_frames} synthetic 11-bit frames ({int(total)} voxels, 4 generated frames x integer "
-                                   "translations), block_size 512, compress+decompress through codec.StreamCodec, random-init weights, q=(0.5,0.5); "
+                                   "translations), block_size 512 (" + ("blocks of a frame coded one after the other" if args.serial_blocks else "the 6-8 blocks of a frame coded as one batched sparse tensor") + "), compress+decompress through codec.StreamCodec, random-init weights, q=(0.5,0.5); "
                                    "a step = the whole sequence", "sharding": f"{world} rank(s), frames assigned largest-first (LPT), no collective",
                        "in_flight": depth, "l2": "every frame (40 MB of input, > 1 GB of intermediates) exceeds the 126 MB L2",
                        "load_imbalance": {"voxels_per_rank": loads, "max_over_mean": max(loads) / (sum(loads) / world),
