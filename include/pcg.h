@@ -251,6 +251,12 @@ int pcg_gdn_fwd_bf16(const float *x, long n, int c, const float *beta, const flo
  * rows of other batches are left untouched. */
 int pcg_topk_mask(const float *logits, const int32_t *coords, long n, int batch, long k, uint8_t *mask,
                   void *scratch, size_t scratch_bytes, void *stream);
+/* The same selection for ALL batch items in one set of passes (n_batches <= 32; h_k: HOST array of n_batches counts; a row's
+ * batch item is its first coordinate; rows of other batch indices are left untouched).  One histogram pass reads every row once
+ * whatever n_batches is; ties at an item's threshold are taken in row order.  scratch >= pcg_topk_mask_batched_scratch_bytes(n). */
+size_t pcg_topk_mask_batched_scratch_bytes(long n);
+int pcg_topk_mask_batched(const float *logits, const int32_t *coords, long n, int n_batches, const long *h_k, uint8_t *mask,
+                          void *scratch, size_t scratch_bytes, void *stream);
 /* Order-preserving row compaction of coords (may be NULL) and features (may be NULL) under mask. */
 int pcg_prune_rows(const int32_t *coords, const float *feats, long n, int c, const uint8_t *mask,
                    int32_t *out_coords, float *out_feats, int32_t *d_n_out, void *scratch,

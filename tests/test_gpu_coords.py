@@ -199,6 +199,28 @@ def test_topk_mask_per_batch(pkg, dev):
             assert logits[sel][mask[sel]].min() >= np.sort(logits[sel])[::-1][k - 1]
 
 
+@pytest.mark.parametrize("n,nb", [(50000, 8), (3000, 2), (400000, 32)])
+def test_topk_mask_batched_equals_per_batch_selection(pkg, dev, n, nb):
+    """pcg_topk_mask_batched (all batch items in one set of radix passes) selects exactly what the single-batch path selects for
+    every item -- including exact ties at the threshold (smaller row first), k = 0, and k larger than the item."""
+    so = pkg.sparse_ops
+    rng = np.random.default_rng(n + nb)
+    logits = rng.standard_normal(n).astype(np.float32)
+    logits[::3] = np.round(logits[::3] * 2) / 2 + 0.0          # many exact ties
+    C = np.zeros((n, 4), np.int32)
+    C[:, 0] = rng.integers(0, nb, n)
+    counts = np.bincount(C[:, 0], minlength=nb)
+    ks = [int(rng.integers(0, c + 1)) for c in counts]
+    ks[0], ks[-1] = 0, int(counts[-1]) + 5
+    lg, Cd = torch.from_numpy(logits).to(dev), to_dev(C, dev)
+    got = so.topk_mask(lg, Cd, ks).cpu().numpy()
+    for b, k in enumerate(ks):
+        sel = np.nonzero(C[:, 0] == b)[0]
+        one = so.topk_mask(lg[torch.from_numpy(sel).to(dev)], to_dev(np.zeros((len(sel), 4), np.int32), dev), [k]).cpu().numpy()
+        assert got[sel].sum() == min(k, len(sel)), (b, k)
+        assert np.array_equal(got[sel], one), f"batch item {b}: batched and single-item selections differ"
+
+
 def test_features_at(pkg, dev):
     so = pkg.sparse_ops
     C = cloud(7, n=800, extent=10)

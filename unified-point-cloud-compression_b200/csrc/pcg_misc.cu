@@ -482,6 +482,149 @@ extern "C" int pcg_topk_mask(const float *logits, const int32_t *coords, long n,
     return pcg_compact(n, FlagTie{logits, coords, batch, s}, EmitTie{s, mask}, d_dummy, cs, st);
 }
 
+// ---------------------------------------------------------------------------- top-k for all batch items at once
+// The same radix select with one TopkState per batch item: a pass reads every row once (its batch index = first coordinate),
+// whatever the number of batch items (a frame coded as B batched blocks, or a training batch, would otherwise pay B x 7 launches
+// and B full passes per level).  Ties at a batch item's threshold are ranked in row order like the single-batch path: one
+// compaction lists the rows whose key equals their item's threshold, and one thread per batch item walks that (normally
+// B-entry) list and takes the first k_rem.
+#define TOPKB_MAX 32
+struct TopkKs {
+    long long k[TOPKB_MAX];
+};
+
+__global__ void k_topkb_init(TopkState *s, TopkKs ks, int nb) {
+    const int b = blockIdx.x;
+    if (b >= nb) return;
+    if (threadIdx.x == 0) { s[b].prefix = 0; s[b].prefix_mask = 0; s[b].k_rem = ks.k[b]; s[b].done = 0; }
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s[b].hist[i] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_topkb_hist(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int nb,
+                                                    int shift, TopkState *s) {
+    __shared__ int h[TOPKB_MAX][256];
+    __shared__ uint32_t s_prefix[TOPKB_MAX], s_pmask[TOPKB_MAX];
+    __shared__ long long suf[257];
+    __shared__ bool last;
+    for (int b = 0; b < nb; ++b) h[b][threadIdx.x] = 0;
+    if (threadIdx.x < nb) { s_prefix[threadIdx.x] = s[threadIdx.x].prefix; s_pmask[threadIdx.x] = s[threadIdx.x].prefix_mask; }
+    __syncthreads();
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const int b = __ldg(coords + 4 * i);
+        if (b < 0 || b >= nb) continue;
+        const uint32_t key = pcg_order_key(__ldg(logits + i));
+        if ((key & s_pmask[b]) == s_prefix[b]) atomicAdd(&h[b][(key >> shift) & 255], 1);
+    }
+    __syncthreads();
+    for (int b = 0; b < nb; ++b)
+        if (h[b][threadIdx.x]) atomicAdd(&s[b].hist[threadIdx.x], h[b][threadIdx.x]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&s[0].done, 1u) == gridDim.x - 1;       // one ticket for the whole pass
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int d = threadIdx.x;
+    for (int b = 0; b < nb; ++b) {
+        const long long cnt = atomicExch(&s[b].hist[d], 0);
+        long long k = s[b].k_rem;
+        __syncthreads();
+        suf[d] = cnt;
+        if (d == 0) suf[256] = 0;
+        __syncthreads();
+        for (int off = 1; off < 256; off <<= 1) {
+            long long add = d + off < 256 ? suf[d + off] : 0;
+            __syncthreads();
+            suf[d] += add;
+            __syncthreads();
+        }
+        if (k > suf[0]) k = suf[0];
+        if (suf[d] >= k && (d == 255 || suf[d + 1] < k)) {
+            s[b].prefix = s_prefix[b] | ((uint32_t)d << shift);
+            s[b].prefix_mask = s_pmask[b] | (255u << shift);
+            s[b].k_rem = k - suf[d + 1];
+        }
+        __syncthreads();
+    }
+    if (d == 0) s[0].done = 0;
+}
+
+__global__ void k_topkb_above(const float *__restrict__ logits, const int32_t *__restrict__ coords, long n, int nb, const TopkState *s,
+                              uint8_t *mask) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = __ldg(coords + 4 * i);
+    if (b < 0 || b >= nb) return;
+    mask[i] = (pcg_order_key(__ldg(logits + i)) > s[b].prefix) ? 1 : 0;
+}
+
+struct FlagTieB {
+    const float *logits;
+    const int32_t *coords;
+    int nb;
+    const TopkState *s;
+    __device__ bool operator()(long i) const {
+        const int b = __ldg(coords + 4 * i);
+        return b >= 0 && b < nb && pcg_order_key(__ldg(logits + i)) == s[b].prefix;
+    }
+};
+struct EmitTieB {
+    int32_t *list;
+    __device__ void operator()(long i, int rank) const { list[rank] = (int)i; }
+};
+
+// thread b walks the (row-ordered) tie list and takes the first k_rem rows of batch item b
+__global__ void k_topkb_ties(const int32_t *__restrict__ list, const int32_t *__restrict__ d_n_ties, const int32_t *__restrict__ coords,
+                             int nb, const TopkState *s, uint8_t *mask) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    long long left = s[b].k_rem;
+    const int n = d_n_ties[0];
+    for (int j = 0; j < n && left > 0; ++j) {
+        const int i = list[j];
+        if (__ldg(coords + 4 * (long)i) == b) { mask[i] = 1; --left; }
+    }
+}
+
+extern "C" size_t pcg_topk_mask_batched_scratch_bytes(long n) {
+    return pcg_compact_scratch_bytes(n) + 256 + TOPKB_MAX * sizeof(TopkState) + 256 + (size_t)(n > 0 ? n : 1) * sizeof(int32_t) + 256;
+}
+
+extern "C" int pcg_topk_mask_batched(const float *logits, const int32_t *coords, long n, int n_batches, const long *h_k, uint8_t *mask,
+                                     void *scratch, size_t scratch_bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    if (n <= 0) return 0;
+    PCG_CHECK_ARG(n_batches >= 1 && n_batches <= TOPKB_MAX && h_k != nullptr && coords != nullptr, "pcg_topk_mask_batched: n_batches=%d must be in [1,%d]", n_batches, TOPKB_MAX);
+    PCG_CHECK_ARG(n < 2147483647L, "pcg_topk_mask_batched: n=%ld exceeds int32", n);
+    PCG_CHECK_ARG(scratch && scratch_bytes >= pcg_topk_mask_batched_scratch_bytes(n), "pcg_topk_mask_batched: scratch too small");
+    TopkKs ks;
+    for (int b = 0; b < TOPKB_MAX; ++b) ks.k[b] = b < n_batches ? (long long)h_k[b] : 0;
+    for (int b = 0; b < n_batches; ++b) PCG_CHECK_ARG(h_k[b] >= 0, "pcg_topk_mask_batched: k[%d]=%ld", b, h_k[b]);
+    PcgScratch cs;
+    pcg_carve_scratch(scratch, scratch_bytes, n, cs);
+    uintptr_t sp = ((uintptr_t)scratch + pcg_compact_scratch_bytes(n) + 255) & ~(uintptr_t)255;
+    TopkState *s = reinterpret_cast<TopkState *>(sp);
+    sp = (sp + TOPKB_MAX * sizeof(TopkState) + 255) & ~(uintptr_t)255;
+    int32_t *d_n_ties = reinterpret_cast<int32_t *>(sp);
+    int32_t *list = reinterpret_cast<int32_t *>(sp + 256);
+    k_topkb_init<<<n_batches, 256, 0, st>>>(s, ks, n_batches);
+    PCG_LAUNCHED();
+    long blocks = cdiv(n, 256 * 4);
+    if (blocks > PCG_SMS * 8) blocks = PCG_SMS * 8;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        k_topkb_hist<<<(unsigned)blocks, 256, 0, st>>>(logits, coords, n, n_batches, shift, s);
+        PCG_LAUNCHED();
+    }
+    k_topkb_above<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(logits, coords, n, n_batches, s, mask);
+    PCG_LAUNCHED();
+    if (int rc = pcg_compact(n, FlagTieB{logits, coords, n_batches, s}, EmitTieB{list}, d_n_ties, cs, st)) return rc;
+    k_topkb_ties<<<1, TOPKB_MAX, 0, st>>>(list, d_n_ties, coords, n_batches, s, mask);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------- features_at_coordinates
 // one warp per query; lanes 0..7 resolve the 8 corners, then all lanes stride the channels
 __global__ void k_features_at(const uint64_t *__restrict__ keys, const int32_t *__restrict__ vals, uint64_t mask,

@@ -803,6 +803,14 @@ def topk_mask(logits, coords, k_per_batch):
     # one entry in k = one batch item in the tensor (transforms.py:228-254 loops over the batch items): no batch filter, so the
     # radix passes read the logits only, not 16 bytes of coordinates per row
     single = len(k_per_batch) == 1
+    if 1 < len(k_per_batch) <= 32:
+        # all batch items in one set of radix passes (a frame coded as batched blocks, a training batch)
+        ks = (ctypes.c_long * len(k_per_batch))(*[int(k) for k in k_per_batch])
+        ws = scratch(lib.pcg_topk_mask_batched_scratch_bytes(n), lg.device)
+        with hbm_span("topk", (n,), (4.0 + 4.0 + 1.0) * n):          # logits + batch index read once, mask written
+            call("pcg_topk_mask_batched", ptr(lg), ptr(coords.contiguous()), n, len(k_per_batch), ctypes.cast(ks, ctypes.c_void_p), ptr(mask),
+                 ptr(ws), ws.numel(), stream())
+        return mask.view(torch.bool)
     for b, k in enumerate(k_per_batch):
         with hbm_span("topk", (n,), 4.0 * n + 1.0 * n):          # logits read once, mask written (the radix passes re-read: not algorithmic)
             call("pcg_topk_mask", ptr(lg), None if single else ptr(coords), n, b, int(k), ptr(mask), ptr(ws), ws.numel(), stream())
