@@ -503,8 +503,13 @@ def run_stream(ctx):
         r = rec.double()
         return (int(rec.shape[0]), float(r[:, :3].sum()), float(torch.round(r[:, 3:] * 255).sum()))
 
+    frame_ms = []
+
     def run(frames_of, keep):
-        return sc.run([(lambda i=i: frames_of(i)) for i in range(n_frames)], sizes=sizes, keep=keep, pipeline=pipe)
+        def timed_keep(rec):                      # host wall clock between consecutive frame completions of this rank (diagnostic)
+            frame_ms.append(time.perf_counter())
+            return keep(rec)
+        return sc.run([(lambda i=i: frames_of(i)) for i in range(n_frames)], sizes=sizes, keep=timed_keep, pipeline=pipe)
 
     with torch.no_grad():
         for i in mine[:2]:                                       # warm-up: allocator pools, packed weights, worker streams
@@ -525,6 +530,9 @@ def run_stream(ctx):
         torch.cuda.synchronize()
         ms_res = e0.elapsed_time(e1)
         launches = pkg._lib.launch_count() - l0
+        stats = torch.cuda.memory_stats(dev)
+        print(f"[bench] rank {rank}: cudaMalloc calls so far {stats.get('num_device_alloc', 0)}, frees {stats.get('num_device_free', 0)}, "
+              f"reserved {stats.get('reserved_bytes.all.peak', 0) / 2**30:.1f} GiB", file=sys.stderr)
         _barrier(ctx)
         clk = clocks.stop() if clocks is not None else None
         # end to end: every frame from pinned host memory, reconstruction back to the host
