@@ -99,7 +99,7 @@ class UnifiedModel(CompressionModel):
         computes every block's result with one set of launches instead of one per block."""
         dev = x_sorted.device
         batch = torch.repeat_interleave(torch.arange(len(counts), dtype=torch.int32, device=dev),
-                                        torch.as_tensor(counts, device=dev))
+                                        torch.as_tensor(counts, device=dev), output_size=int(sum(counts)))
         coords0, _ = so.gather_block(x_sorted)
         order = so.sort_rows_i32(coords0, morton=True, bits=so.LOCALITY_BITS)      # blocks are disjoint cubes: global Z-order keeps them apart
         coords4, feats = so.gather_block(x_sorted, order)
