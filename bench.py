@@ -512,10 +512,15 @@ def run_stream(ctx):
         return sc.run([(lambda i=i: frames_of(i)) for i in range(n_frames)], sizes=sizes, keep=timed_keep, pipeline=pipe)
 
     with torch.no_grad():
-        for i in mine[:2]:                                       # warm-up: allocator pools, packed weights, worker streams
+        # warm-up: packed weights, worker streams, and the caching allocator's pools -- one frame of every distinct size this rank
+        # will see, largest first, on every worker stream (a first-seen larger frame costs cudaMalloc calls of GB-sized blocks:
+        # 40-58 Mpoints/s from run to run before this)
+        warm = sorted({sizes[i]: i for i in mine}.values(), key=lambda i: -sizes[i])
+        for i in warm[:1]:
             sc.code_frame(resident[i])
         if pipe is not None:
-            pipe.map(lambda i: sc.code_frame(resident[i]), mine[:depth])
+            for _ in range(2):
+                pipe.map(lambda i: sc.code_frame(resident[i]), [w for w in warm for _ in range(depth)])
         codec_mod.gather_results({-1 - rank: (0, 0.0, 0.0)}, world, rank)      # warm-up of the result gather (first object collective: ~1 s of set-up)
         _barrier(ctx)
         clocks = ClockSampler(range(world)) if rank == 0 else None
