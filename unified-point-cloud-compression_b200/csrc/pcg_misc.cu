@@ -575,16 +575,31 @@ struct EmitTieB {
     __device__ void operator()(long i, int rank) const { list[rank] = (int)i; }
 };
 
-// thread b walks the (row-ordered) tie list and takes the first k_rem rows of batch item b
-__global__ void k_topkb_ties(const int32_t *__restrict__ list, const int32_t *__restrict__ d_n_ties, const int32_t *__restrict__ coords,
-                             int nb, const TopkState *s, uint8_t *mask) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= nb) return;
-    long long left = s[b].k_rem;
+// CTA b walks the (row-ordered) tie list in chunks of 256 and takes the first k_rem rows of batch item b: rank of an entry =
+// ties of item b before it (running count + ballot ranks inside the chunk); stops as soon as k_rem are taken
+__global__ void __launch_bounds__(256) k_topkb_ties(const int32_t *__restrict__ list, const int32_t *__restrict__ d_n_ties,
+                                                    const int32_t *__restrict__ coords, const TopkState *s, uint8_t *mask) {
+    __shared__ int warp_cnt[8];
+    const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long want = s[b].k_rem;
     const int n = d_n_ties[0];
-    for (int j = 0; j < n && left > 0; ++j) {
-        const int i = list[j];
-        if (__ldg(coords + 4 * (long)i) == b) { mask[i] = 1; --left; }
+    long long taken = 0;
+    for (int base = 0; base < n && taken < want; base += 256) {
+        const int j = base + threadIdx.x;
+        const int i = j < n ? list[j] : -1;
+        const bool mine = i >= 0 && __ldg(coords + 4 * (long)i) == b;
+        const unsigned bal = __ballot_sync(0xffffffffu, mine);
+        if (lane == 0) warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            if (w < warp) before += warp_cnt[w];
+            total += warp_cnt[w];
+        }
+        if (mine && taken + before + __popc(bal & ((1u << lane) - 1u)) < want) mask[i] = 1;
+        taken += total;
+        __syncthreads();
     }
 }
 
@@ -620,7 +635,7 @@ extern "C" int pcg_topk_mask_batched(const float *logits, const int32_t *coords,
     k_topkb_above<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(logits, coords, n, n_batches, s, mask);
     PCG_LAUNCHED();
     if (int rc = pcg_compact(n, FlagTieB{logits, coords, n_batches, s}, EmitTieB{list}, d_n_ties, cs, st)) return rc;
-    k_topkb_ties<<<1, TOPKB_MAX, 0, st>>>(list, d_n_ties, coords, n_batches, s, mask);
+    k_topkb_ties<<<n_batches, 256, 0, st>>>(list, d_n_ties, coords, s, mask);
     PCG_LAUNCHED();
     return 0;
 }
