@@ -42,11 +42,16 @@ class SortedMinkowskiLeakyReLU(ME.MinkowskiLeakyReLU):
 
 def sort_tensor(x):
     """Rows in lexicographic (b,x,y,z) order -- defines the symbol order of the bitstream (utils.py:142-165)."""
+    if x.F.is_cuda and x.F.dtype == torch.float32 and not (torch.is_grad_enabled() and x.F.requires_grad):
+        oc, of = so.gather_rows(x.C, x.F, so.sort_rows_i32(x.C, morton=False))       # coordinates and features in one pass
+        return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
     perm = so.lexsort(x.C)
     return ME.SparseTensor(x.F[perm], _coord_set=so.CoordSet(x.C[perm], x.coord_set.ts))
 
 
 def sort_points(points):
+    if points.is_cuda and points.dtype == torch.int32:
+        return so.gather_rows(points, None, so.sort_rows_i32(points, morton=False))[0]
     return points[so.lexsort(points.to(torch.int32))]
 
 
@@ -122,6 +127,22 @@ class MeanScaleHyperprior(CompressionModel):
         if not self.adaptive_BN:
             one = torch.ones((1, C, n_rows), device=device)
             return one, one
+        if not torch.is_grad_enabled():
+            # inference: the gain vectors depend on (q, MLP weights) only -- computed once per q tensor / weight version instead of
+            # ~20 tiny launches per frame; one quality setting for the whole tensor (q has one row) needs no per-row gather either
+            key = (q.data_ptr(), q._version, tuple(q.shape), tuple(p._version for p in self.scale_nn.parameters()),
+                   tuple(p._version for p in self.rescale_nn.parameters()))
+            hit = getattr(self, "_gain_cache", None)
+            if hit is None or hit[0] != key:
+                scale_b = self.scale_nn(q) + self.eps
+                hit = (key, scale_b, 1.0 / scale_b if self.inverse_rescaling else 1.0 / self.rescale_nn(q))
+                self._gain_cache = hit
+            scale_b, rescale_b = hit[1], hit[2]
+            if q.shape[0] == 1:
+                view = lambda t: t[0].view(1, C, 1).expand(1, C, n_rows)
+            else:
+                view = lambda t: t[batch_idx].t().unsqueeze(0)
+            return view(scale_b), (view(rescale_b) if need_rescale else None)
         scale_b = self.scale_nn(q) + self.eps                       # (B, C)
         scale = scale_b[batch_idx].t().unsqueeze(0)                 # view (1, C, N)
         rescale = None
