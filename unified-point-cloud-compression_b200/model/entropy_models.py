@@ -131,12 +131,12 @@ class MeanScaleHyperprior(CompressionModel):
         if not torch.is_grad_enabled():
             # inference: the gain vectors depend on (q, MLP weights) only -- computed once per q tensor / weight version instead of
             # ~20 tiny launches per frame; one quality setting for the whole tensor (q has one row) needs no per-row gather either
-            key = (q.data_ptr(), q._version, tuple(q.shape), tuple(p._version for p in self.scale_nn.parameters()),
-                   tuple(p._version for p in self.rescale_nn.parameters()))
+            # (keyed on the q tensor OBJECT, which the cache keeps alive: an address alone could be recycled for another q)
+            key = (q._version, tuple(p._version for p in self.scale_nn.parameters()), tuple(p._version for p in self.rescale_nn.parameters()))
             hit = getattr(self, "_gain_cache", None)
-            if hit is None or hit[0] != key:
+            if hit is None or hit[3] is not q or hit[0] != key:
                 scale_b = self.scale_nn(q) + self.eps
-                hit = (key, scale_b, 1.0 / scale_b if self.inverse_rescaling else 1.0 / self.rescale_nn(q))
+                hit = (key, scale_b, 1.0 / scale_b if self.inverse_rescaling else 1.0 / self.rescale_nn(q), q)
                 self._gain_cache = hit
             scale_b, rescale_b = hit[1], hit[2]
             if q.shape[0] == 1:
