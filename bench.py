@@ -196,7 +196,7 @@ def main():
     import torch.distributed as dist
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback for the graft)"
-    if world > 1 and os.environ.get("PCG_PIN", "0") == "1":
+    if world > 1 and os.environ.get("PCG_PIN", "1") == "1":
         # one slice of the host cores per rank: every rank runs a launching thread per frame in flight, and 8 ranks x 3 threads
         # migrating over 16 cores cost ~6 % of the 8-GPU throughput in round 1 (host enqueue is 80 % of a step's wall time)
         cores = sorted(os.sched_getaffinity(0))

@@ -246,6 +246,9 @@ int pcg_gdn_fwd(const float *x, long n, int c, const float *beta, const float *g
 int pcg_gdn_fwd_bf16(const float *x, long n, int c, const float *beta, const float *gamma, int inverse, float *out, void *out_bf16,
                      void *stream);
 
+/* Decoder output rows (model/model.py:247-250): out[i] = [x, y, z, clamp(round(f * 255), 0, 255) / 255], (n, 3 + c) fp32. */
+int pcg_finalize(const int32_t *coords, const float *feats, int c, long n, float *out, void *stream);
+
 /* ---- occupancy top-k + prune (transforms.py:228-282, ME.MinkowskiPruning ME5) ---------------
  * mask[i] = 1 for the k rows of batch `batch` with the largest logits (ties: smaller row first);
  * rows of other batches are left untouched. */

@@ -62,6 +62,7 @@ _PROTOS = {
     "pcg_activation": (_I, [_P, _L, _I, _P, _P]),
     "pcg_gdn_fwd": (_I, [_P, _L, _I, _P, _P, _I, _P, _P]),
     "pcg_gdn_fwd_bf16": (_I, [_P, _L, _I, _P, _P, _I, _P, _P, _P]),
+    "pcg_finalize": (_I, [_P, _P, _I, _L, _P, _P]),
     "pcg_topk_mask": (_I, [_P, _P, _L, _I, _L, _P, _P, _SZ, _P]),
     "pcg_topk_mask_batched_scratch_bytes": (_SZ, [_L]),
     "pcg_topk_mask_batched": (_I, [_P, _P, _L, _I, _P, _P, _P, _SZ, _P]),

@@ -482,6 +482,26 @@ extern "C" int pcg_topk_mask(const float *logits, const int32_t *coords, long n,
     return pcg_compact(n, FlagTie{logits, coords, batch, s}, EmitTie{s, mask}, d_dummy, cs, st);
 }
 
+// ---------------------------------------------------------------------------- decoder output rows
+// out[i] = [x, y, z, clamp(round(f * 255), 0, 255) / 255] (model/model.py:247-250: 8-bit colours kept as floats; round = half to
+// even like torch.round, true division like torch's `/ 255`).  One pass instead of round / clamp / div / cast / cat.
+__global__ void k_finalize(const int32_t *__restrict__ coords, const float *__restrict__ feats, int c, long n, float *__restrict__ out) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int4 p = pcg_ld_coord(coords, i);
+    float *o = out + i * (3 + c);
+    o[0] = (float)p.y; o[1] = (float)p.z; o[2] = (float)p.w;
+    for (int j = 0; j < c; ++j) o[3 + j] = fminf(fmaxf(rintf(__ldg(feats + i * c + j) * 255.0f), 0.0f), 255.0f) / 255.0f;
+}
+
+extern "C" int pcg_finalize(const int32_t *coords, const float *feats, int c, long n, float *out, void *stream) {
+    PCG_CHECK_ARG(c >= 1 && c <= 16, "pcg_finalize: c=%d", c);
+    if (n <= 0) return 0;
+    k_finalize<<<(unsigned)cdiv(n, 256), 256, 0, as_stream(stream)>>>(coords, feats, c, n, out);
+    PCG_LAUNCHED();
+    return 0;
+}
+
 // ---------------------------------------------------------------------------- top-k for all batch items at once
 // The same radix select with one TopkState per batch item: a pass reads every row once (its batch index = first coordinate),
 // whatever the number of batch items (a frame coded as B batched blocks, or a training batch, would otherwise pay B x 7 launches

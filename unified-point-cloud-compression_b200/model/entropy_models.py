@@ -42,11 +42,16 @@ class SortedMinkowskiLeakyReLU(ME.MinkowskiLeakyReLU):
 
 def sort_tensor(x):
     """Rows in lexicographic (b,x,y,z) order -- defines the symbol order of the bitstream (utils.py:142-165)."""
+    if x.F.is_cuda and x.F.dtype == torch.float32 and not (torch.is_grad_enabled() and x.F.requires_grad):
+        oc, of = so.gather_rows(x.C, x.F, so.sort_rows_i32(x.C, morton=False))       # coordinates and features in one pass
+        return ME.SparseTensor(of, _coord_set=so.CoordSet(oc, x.coord_set.ts))
     perm = so.lexsort(x.C)
     return ME.SparseTensor(x.F[perm], _coord_set=so.CoordSet(x.C[perm], x.coord_set.ts))
 
 
 def sort_points(points):
+    if points.is_cuda and points.dtype == torch.int32:
+        return so.gather_rows(points, None, so.sort_rows_i32(points, morton=False))[0]
     return points[so.lexsort(points.to(torch.int32))]
 
 
@@ -117,11 +122,31 @@ class MeanScaleHyperprior(CompressionModel):
         return self.quant_nn(torch.stack((scale.expand_as(stddev), stddev), dim=3)).squeeze(dim=3)
 
     def _gains(self, q, batch_idx, n_rows, device, need_rescale):
-        """(scale, rescale) as (1,C,N) views, gathered per row by batch index (a9)."""
+        """(scale, rescale) as (1,C,N) views, gathered per row by batch index (a9).  batch_idx: tensor, or a callable that
+        produces it (only evaluated when several quality settings share the tensor)."""
         C = self.scale_nn[-2].out_features
         if not self.adaptive_BN:
             one = torch.ones((1, C, n_rows), device=device)
             return one, one
+        if not torch.is_grad_enabled():
+            # inference: the gain vectors depend on (q, MLP weights) only -- computed once per q tensor / weight version instead of
+            # ~20 tiny launches per frame; one quality setting for the whole tensor (q has one row) needs no per-row gather either
+            # (keyed on the q tensor OBJECT, which the cache keeps alive: an address alone could be recycled for another q)
+            key = (q._version, tuple(p._version for p in self.scale_nn.parameters()), tuple(p._version for p in self.rescale_nn.parameters()))
+            hit = getattr(self, "_gain_cache", None)
+            if hit is None or hit[3] is not q or hit[0] != key:
+                scale_b = self.scale_nn(q) + self.eps
+                hit = (key, scale_b, 1.0 / scale_b if self.inverse_rescaling else 1.0 / self.rescale_nn(q), q)
+                self._gain_cache = hit
+            scale_b, rescale_b = hit[1], hit[2]
+            if q.shape[0] == 1:
+                view = lambda t: t[0].view(1, C, 1).expand(1, C, n_rows)
+            else:
+                bi = batch_idx() if callable(batch_idx) else batch_idx
+                view = lambda t: t[bi].t().unsqueeze(0)
+            return view(scale_b), (view(rescale_b) if need_rescale else None)
+        if callable(batch_idx):
+            batch_idx = batch_idx()
         scale_b = self.scale_nn(q) + self.eps                       # (B, C)
         scale = scale_b[batch_idx].t().unsqueeze(0)                 # view (1, C, N)
         rescale = None
@@ -191,7 +216,7 @@ class MeanScaleHyperprior(CompressionModel):
         z_sym = eb.quantize(z_feats, "symbols", med)
         z_hat = ME.SparseTensor(eb.dequantize(z_sym, med.expand_as(z_feats))[0].t(), _coord_set=z.coord_set)
         scales_hat, means_hat = self._hyper_synthesis(z_hat, y.C)
-        scale, _ = self._gains(q, y.C[:, 0].long(), y.F.shape[0], y.device, False)
+        scale, _ = self._gains(q, lambda: y.C[:, 0].long(), y.F.shape[0], y.device, False)
         indexes = gc.build_indexes(scales_hat * scale)
         y_sym = gc.quantize(y.F.t().unsqueeze(0) * scale, "symbols", means_hat * scale)
         return {"y_points": y.C, "z_points": z.C, "z_symbols": z_sym, "y_symbols": y_sym, "y_indexes": indexes}
@@ -223,7 +248,7 @@ class MeanScaleHyperprior(CompressionModel):
         z_hat_f = eb.dequantize(z_symbols, med.expand(z_symbols.shape))
         z_hat = ME.SparseTensor(z_hat_f[0].t(), z_points.to(torch.int32), tensor_stride=32, device=z_points.device)
         scales_hat, means_hat = self._hyper_synthesis(z_hat, y_points)
-        scale, rescale = self._gains(q, y_points[:, 0].long(), y_points.shape[0], y_points.device, True)
+        scale, rescale = self._gains(q, lambda: y_points[:, 0].long(), y_points.shape[0], y_points.device, True)
         indexes = gc.build_indexes(scales_hat * scale)
         sym = y_symbol_source(indexes)
         if self.quantization_offset:

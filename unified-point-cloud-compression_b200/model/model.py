@@ -248,5 +248,9 @@ class UnifiedModel(CompressionModel):
     @staticmethod
     def finalize(coords, feats):
         """8-bit colour rounding + [xyz|rgb] rows (model.py:247-250)."""
+        if feats.is_cuda and feats.dtype == torch.float32 and coords.dtype == torch.int32 and not (torch.is_grad_enabled() and feats.requires_grad):
+            out = torch.empty((feats.shape[0], 3 + feats.shape[1]), dtype=torch.float32, device=feats.device)
+            so._lib.call("pcg_finalize", so.ptr(coords.contiguous()), so.ptr(feats.contiguous()), feats.shape[1], feats.shape[0], so.ptr(out), so.stream())
+            return out
         rgb = torch.clamp(torch.round(feats * 255), 0.0, 255.0) / 255
         return torch.cat([coords[:, 1:4].to(rgb.dtype), rgb], dim=1)
