@@ -329,90 +329,6 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
     }
 }
 
-// ---------------------------------------------------------------------------- cell-per-lane-group variant (default)
-// k_cells_reduce above gives every child slot its own lanes and walks ALL present parents: a parent reaches 1, 2, 4 or 8 of the 8
-// children, so ~58 % of the lanes are predicated off in every step and the kernel is bound by issue slots (ncu: 60-76 % SM
-// busy at 40 % of the DRAM bandwidth).  Here a group of LPR = cout / 4 lanes owns ONE CELL with all of its 8 children: lane t of the
-// group keeps channels 4t..4t+3 of the 8 child rows in 32 registers, the loop runs over the cell's present parents, and which
-// children a parent reaches depends on e alone -- a group-uniform predicate, so no lane idles inside a step and the loads of one
-// (parent, child) pair are one contiguous 2 * cout-byte run of T.  Same fixed order (e ascending) per element: same bits.
-template <int LPR>
-__global__ void __launch_bounds__(256) k_cells_reduce2(const __nv_bfloat16 *__restrict__ T, const int32_t *__restrict__ pnbr, long pitch,
-                                                       const uint8_t *__restrict__ cell_mask, const int32_t *__restrict__ cell_base,
-                                                       long n_cells, const float *__restrict__ bias, int act, float *__restrict__ out_f32,
-                                                       __nv_bfloat16 *__restrict__ out_bf16) {
-    constexpr int G = 32 / LPR;                     // cells per warp
-    constexpr int COUT = 4 * LPR;
-    constexpr int NJ = (27 + LPR - 1) / LPR;        // parent-list entries per lane
-    const int lane = threadIdx.x & 31, grp = lane / LPR, t = lane % LPR;
-    const long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long n_warps = ((long)gridDim.x * blockDim.x) >> 5;
-    const long t_row = (long)125 * COUT;
-    for (long c0 = warp * G; c0 < n_cells; c0 += n_warps * G) {
-        const long cell = c0 + grp;
-        const bool live = cell < n_cells;
-        int pr[NJ];
-        uint32_t present = 0;
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-            const int e = t + LPR * j;
-            pr[j] = (live && e < 27) ? __ldg(pnbr + (long)e * pitch + cell) : -1;
-            const uint32_t bal = __ballot_sync(0xffffffffu, pr[j] >= 0);
-            present |= ((bal >> (grp * LPR)) & (uint32_t)((1ull << LPR) - 1ull)) << (LPR * j);
-        }
-        const uint32_t cmask = live ? cell_mask[cell] : 0u;
-        float acc[8][4];
-#pragma unroll
-        for (int b = 0; b < 8; ++b)
-#pragma unroll
-            for (int q = 0; q < 4; ++q) acc[b][q] = 0.f;
-        // every group walks its own list; the warp iterates until the longest list is done (shuffles need all lanes)
-        while (__any_sync(0xffffffffu, present != 0u)) {
-            const int e = present ? __ffs(present) - 1 : 0;
-            const bool on = present != 0u;
-            present &= present - 1;
-            int p = -1;
-#pragma unroll
-            for (int j = 0; j < NJ; ++j) {
-                const int v = __shfl_sync(0xffffffffu, pr[j], grp * LPR + e % LPR);      // lane t = e % LPR of the group holds entry e in pr[e / LPR]
-                if (e / LPR == j) p = v;
-            }
-            if (!on || p < 0) continue;
-            const int ex = e % 3, ey = (e / 3) % 3, ez = e / 9;                  // 0..2 = offsets -1..1
-            const __nv_bfloat16 *trow = T + (long)p * t_row + t * 4;
-#pragma unroll
-            for (int b = 0; b < 8; ++b) {
-                const int bx = b & 1, by = (b >> 1) & 1, bz = (b >> 2) & 1;
-                if ((bx && ex == 0) || (by && ey == 0) || (bz && ez == 0)) continue;      // odd child bit: parents at e = 0, +1 only
-                const int k = (bx - 2 * (ex - 1) + 2) + 5 * (by - 2 * (ey - 1) + 2) + 25 * (bz - 2 * (ez - 1) + 2);
-                const uint2 w = __ldg(reinterpret_cast<const uint2 *>(trow + (long)k * COUT));
-                acc[b][0] += __uint_as_float(w.x << 16);
-                acc[b][1] += __uint_as_float(w.x & 0xFFFF0000u);
-                acc[b][2] += __uint_as_float(w.y << 16);
-                acc[b][3] += __uint_as_float(w.y & 0xFFFF0000u);
-            }
-        }
-        if (!live) continue;
-        const int cbase = __ldg(cell_base + cell);
-        float bv[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) bv[q] = bias ? __ldg(bias + t * 4 + q) : 0.f;
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-            if (!((cmask >> b) & 1u)) continue;
-            const long o = (long)cbase + __popc(cmask & ((1u << b) - 1u));
-            float f[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) f[q] = pcg_apply_act(acc[b][q] + bv[q], act);
-            if (out_f32) *reinterpret_cast<float4 *>(out_f32 + o * COUT + t * 4) = make_float4(f[0], f[1], f[2], f[3]);
-            if (out_bf16) {
-                __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
-                *reinterpret_cast<uint2 *>(out_bf16 + o * COUT + t * 4) = make_uint2(*reinterpret_cast<uint32_t *>(&h0), *reinterpret_cast<uint32_t *>(&h1));
-            }
-        }
-    }
-}
-
 extern "C" int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnbr, long pnbr_pitch, const uint8_t *cell_mask,
                                 const int32_t *cell_base, long n_cells, const float *bias, int act, float *out_f32, void *out_bf16,
                                 void *stream) {
@@ -422,18 +338,6 @@ extern "C" int pcg_cells_reduce(const void *t_bf16, int cout, const int32_t *pnb
     cudaStream_t st = as_stream(stream);
     const __nv_bfloat16 *T = reinterpret_cast<const __nv_bfloat16 *>(t_bf16);
     __nv_bfloat16 *ob = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
-    static const int variant = getenv("PCG_REDUCE") ? atoi(getenv("PCG_REDUCE")) : 2;        // 1 = child-slot kernel (A/B), 2 = cell-per-lane-group
-    if (variant == 2 && cout <= 128) {
-        const int lpr = cout / 4, cells_per_block = 8 * (32 / lpr);
-        long nb2 = cdiv(n_cells, cells_per_block);
-        if (nb2 > (long)PCG_SMS * 64) nb2 = (long)PCG_SMS * 64;
-        const unsigned b2 = (unsigned)nb2;
-        if (lpr == 32) k_cells_reduce2<32><<<b2, 256, 0, st>>>(T, pnbr, pnbr_pitch, cell_mask, cell_base, n_cells, bias, act, out_f32, ob);
-        else if (lpr == 16) k_cells_reduce2<16><<<b2, 256, 0, st>>>(T, pnbr, pnbr_pitch, cell_mask, cell_base, n_cells, bias, act, out_f32, ob);
-        else k_cells_reduce2<8><<<b2, 256, 0, st>>>(T, pnbr, pnbr_pitch, cell_mask, cell_base, n_cells, bias, act, out_f32, ob);
-        PCG_LAUNCHED();
-        return 0;
-    }
     const int lanes = cout / 8;
     long nb = cdiv(n_cells * 8 * lanes, 256);
     static const long cap_blocks = getenv("PCG_REDUCE_BLOCKS") ? atol(getenv("PCG_REDUCE_BLOCKS")) : (long)PCG_SMS * 5 * 8;   // 8 units per warp at 5 blocks/SM
