@@ -232,10 +232,6 @@ extern "C" int pcg_cells_kernel_map3(const uint64_t *cell_keys, const int32_t *c
 // pnbr[e][cell]), ballots which parents exist and walks only those -- a warp-uniform loop, four parents per batch so
 // that four independent 16-byte loads of T are in flight per lane; whether parent e reaches child b is a per-lane
 // predicate, not a branch.
-// ke(e) = -2 ex - 10 ey - 50 ez for e = (ex+1) + 3 (ey+1) + 9 (ez+1); entries 27..31 serve the padding index 31 of a short batch
-__constant__ int c_cells_ke[32] = {62, 60, 58, 52, 50, 48, 42, 40, 38, 12, 10, 8, 2, 0, -2, -8, -10, -12, -38, -40, -42, -48, -50, -52, -58, -60, -62,
-                                   0, 0, 0, 0, 0};
-
 template <int LANES>
 __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__restrict__ T, int cout, const int32_t *__restrict__ pnbr,
                                                       long pitch, const uint8_t *__restrict__ cell_mask,
@@ -268,7 +264,6 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
 
         const int b = (int)(unit % WPC) * CPW + lane / LANES;
         const int bx = b & 1, by = (b >> 1) & 1, bz = (b >> 2) & 1;
-        const int kb = (bx + 2) + 5 * (by + 2) + 25 * (bz + 2);       // k(b, e) = kb + ke(e), ke(e) = -2 ex - 10 ey - 50 ez
         uint32_t present = __ballot_sync(0xffffffffu, my_prow >= 0);
         const bool exists = (cmask >> b) & 1u;
         const uint32_t reach = exists ? cells_valid_e(b) : 0u;      // parents e that reach child b
@@ -289,7 +284,8 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int k = kb + c_cells_ke[e[u]];            // e is warp-uniform: one uniform constant load instead of the div / mod chain
+                const int ex = e[u] % 3 - 1, ey = (e[u] / 3) % 3 - 1, ez = e[u] / 9 - 1;
+                const int k = (bx - 2 * ex + 2) + 5 * (by - 2 * ey + 2) + 25 * (bz - 2 * ez + 2);
                 const bool ok = pr[u] >= 0 && ((reach >> e[u]) & 1u);
                 v[u] = ok ? __ldg(reinterpret_cast<const uint4 *>(T + (long)pr[u] * t_row + (long)k * cout) + part) : make_uint4(0, 0, 0, 0);
                 if (!ok) pr[u] = -1;
