@@ -267,9 +267,6 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
         uint32_t present = __ballot_sync(0xffffffffu, my_prow >= 0);
         const bool exists = (cmask >> b) & 1u;
         const uint32_t reach = exists ? cells_valid_e(b) : 0u;      // parents e that reach child b
-        // parents that reach none of this warp's (existing) child slots are not walked at all: with two slots per warp (cout = 128)
-        // the union is 12-27 of the 27 offsets, and nothing when neither child exists (same ascending-e order for the rest)
-        present &= __reduce_or_sync(0xffffffffu, reach);
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
