@@ -22,10 +22,9 @@ __global__ void __launch_bounds__(256) k_conv_bwd_weight(const float *__restrict
     dw += (size_t)slice * K * cin * cout;
     const int tid = threadIdx.x, ci = tid >> 4, cq = (tid & 15) * 4;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    const long tiles_all = (n_out + BW_ROWS - 1) / BW_ROWS;
-    const long t_begin = (long)slice * tiles_per_slice;
-    const long tiles = t_begin + tiles_per_slice < tiles_all ? t_begin + tiles_per_slice : tiles_all;
-    for (long t = t_begin; t < tiles; ++t) {
+    const long tiles = (n_out + BW_ROWS - 1) / BW_ROWS;
+    const long n_slices = gridDim.x / K;            // slice s = tiles s, s + S, ... (interleaved, see k_conv_bwd_weight_tc)
+    for (long t = slice; t < tiles; t += n_slices) {
         if (tile_mask && !((__ldg(tile_mask + t * 4 + (k >> 5)) >> (k & 31)) & 1u)) continue;     // uniform
         const long o0 = t * BW_ROWS;
         if (tid < BW_ROWS) idx_s[tid] = (o0 + tid < n_out) ? __ldg(nbr + (long)k * pitch + o0 + tid) : -1;
@@ -161,8 +160,9 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int k = blockIdx.x;
-    const long t0 = (long)blockIdx.y * p.tiles_per_slice;
-    const long t1 = t0 + p.tiles_per_slice < p.tiles ? t0 + p.tiles_per_slice : p.tiles;
+    // slice s = tiles s, s + S, s + 2S, ... (interleaved: with class-major row orders an offset is only active in one contiguous
+    // range of tiles, which a contiguous split would hand to a single slice)
+    const long t0 = blockIdx.y, t1 = p.tiles, tstep = gridDim.y;
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
         const uint8_t *fsrc = p.feats + (lane & 7) * 16, *gsrc = p.gout + (lane & 7) * 16;
         int s = 0;
         uint32_t wrap = 0;
-        for (long t = t0; t < t1; ++t) {
+        for (long t = t0; t < t1; t += tstep) {
             if (!active(t)) continue;                                          // warp-uniform
             int idx_f[4], idx_g[4];
 #pragma unroll
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.n_mma >> 3) << 17) | ((128u >> 4) << 24);
         int s = 0;
         uint32_t ph = 0, started = 0;
-        for (long t = t0; t < t1; ++t) {
+        for (long t = t0; t < t1; t += tstep) {
             if (!active(t)) continue;
             mbar_wait(smem_u32(full_bar + s), ph);
             fence_proxy_async();                      // cp.async wrote the images through the generic proxy
