@@ -27,6 +27,16 @@ for _ in range(2):
 torch.cuda.synchronize()
 import time
 t0 = time.perf_counter(); tr.step(dc, df, q); torch.cuda.synchronize(); print(f"step wall {1e3 * (time.perf_counter() - t0):.1f} ms, {len(c)} voxels")
+so = pkg.sparse_ops
+so.profiler = so.ConvProfiler()
+tr.step(dc, df, q)
+summ = so.profiler.summary()
+so.profiler = None
+for kind, d in sorted(summ.items(), key=lambda kv: -kv[1]["ms"]):
+    print(f"{kind:24s} {d['launches']:4d} launches {d['ms']:9.3f} ms  {d['flops'] / max(d['ms'], 1e-9) / 1e9:8.1f} TFLOP/s")
+    if kind in ("conv_bwd_weight", "conv_tc"):
+        for shape, v in sorted(d["by_shape"].items(), key=lambda kv: -kv[1][1]):
+            print(f"    {str(shape):32s} x{v[0]} {v[1]:8.3f} ms {v[2] / max(v[1], 1e-9) / 1e9:8.1f} TFLOP/s")
 from torch.profiler import ProfilerActivity, profile
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     tr.step(dc, df, q)

@@ -63,6 +63,10 @@ class _SparseConv(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             nbr, tmask = in_set.kernel_map(out_set, ksize, transposed)
             dw = torch.empty_like(w3)
+            prof = so.profiler
+            if prof is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             if bwd_weight_tc_eligible(K, cin, cout) and tmask is not None and out_set.n > 0 and feats.shape[0] > 0:
                 # tensor cores: bf16 operand rows of F (cached shadow of the forward pass when there is one) and of G
                 fb = so.to_bf16(feats) if cin >= 33 else _bf16_rows64(feats)
@@ -76,6 +80,11 @@ class _SparseConv(torch.autograd.Function):
                 ws = so.scratch(nb, g.device) if nb else None
                 call("pcg_conv_bwd_weight_f32_sliced", ptr(feats.contiguous()), cin, ptr(nbr), nbr.shape[1], ptr(tmask), K, out_set.n, ptr(g), cout,
                      ptr(ws), nb, ptr(dw), stream())
+            if prof is not None:
+                e1.record()
+                pairs = prof.pairs(nbr)
+                prof.records.append(("conv_bwd_weight", (K, cin, cout, int(out_set.n)), 2.0 * pairs * cin * cout,
+                                     2.0 * pairs * (cin + cout) + 4.0 * K * cin * cout, e0, e1))
             g_weight = dw.view_as(weight)
         if has_bias and ctx.needs_input_grad[2]:
             g_bias = g.sum(dim=0, keepdim=True)
