@@ -145,6 +145,29 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t saddr, uint32_t 
     return d;
 }
 
+// Warp-wide iterator over the ACTIVE tiles of a slice (tiles t0, t0 + step, ... whose mask bit k is set): the masks of the next 32
+// candidate tiles are fetched by the 32 lanes at once, so the walk costs one dependent global load per 32 tiles instead of one per
+// tile (the per-tile mask and index loads were ~1.5 us of exposed latency per tile on the 88 k-tile head layers).
+struct BwtTileIter {
+    const uint32_t *mask;
+    long next_base, cur_base, t1, step;
+    uint32_t bits;
+    int word, bit;
+    __device__ __forceinline__ long next(int lane) {         // call with the whole warp; returns -1 at the end
+        while (bits == 0u) {
+            if (next_base >= t1) return -1;
+            const long t = next_base + (long)lane * step;
+            const bool a = t < t1 && ((__ldg(mask + t * 4 + word) >> bit) & 1u);
+            bits = __ballot_sync(0xffffffffu, a);
+            cur_base = next_base;
+            next_base += 32 * step;
+        }
+        const int j = __ffs(bits) - 1;
+        bits &= bits - 1;
+        return cur_base + (long)j * step;
+    }
+};
+
 __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -181,7 +204,6 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_d = *tmem_slot;
-    auto active = [&](long t) -> bool { return (__ldg(p.tile_mask + t * 4 + (k >> 5)) >> (k & 31)) & 1u; };
     const int m_blocks = p.ci_chunks_p / 2;
 
     if (warp < 4) {
@@ -190,13 +212,21 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
         const uint8_t *fsrc = p.feats + (lane & 7) * 16, *gsrc = p.gout + (lane & 7) * 16;
         int s = 0;
         uint32_t wrap = 0;
-        for (long t = t0; t < t1; t += tstep) {
-            if (!active(t)) continue;                                          // warp-uniform
-            int idx_f[4], idx_g[4];
+        BwtTileIter it{p.tile_mask, t0, t0, t1, tstep, 0u, k >> 5, k & 31};
+        auto load_idx = [&](long t, int (&idx)[4]) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) idx[u] = __ldg(p.nbr + (long)k * p.pitch + t * BWT_ROWS + lane + 32 * u);   // padded with -1 to 128 rows
+        };
+        int idx_f[4], idx_n[4];
+        long t = it.next(lane);
+        if (t >= 0) load_idx(t, idx_f);
+        while (t >= 0) {
+            const long tn = it.next(lane);
+            if (tn >= 0) load_idx(tn, idx_n);                                    // next tile's indices in flight under this tile's gathers
+            int idx_g[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const long o = t * BWT_ROWS + lane + 32 * u;
-                idx_f[u] = __ldg(p.nbr + (long)k * p.pitch + o);               // the table is padded with -1 to a multiple of 128 rows
                 idx_g[u] = (o < p.n_out && idx_f[u] >= 0) ? (int)o : -1;
             }
             const uint32_t fb = smem_u32(full_bar + s);
@@ -212,34 +242,42 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
                 asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
             }
             if (++s == p.stages) { s = 0; ++wrap; }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) idx_f[u] = idx_n[u];
+            t = tn;
         }
-    } else if (lane == 0) {
-        // ------------------------------------------------------------------ MMA issuer
+    } else {
+        // ------------------------------------------------------------------ MMA issuer (the warp walks the tiles, lane 0 issues)
         // idesc: fp32 accumulate, bf16 x bf16, A and B MN-major (bits 15 / 16), N, M = 128
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.n_mma >> 3) << 17) | ((128u >> 4) << 24);
         int s = 0;
         uint32_t ph = 0, started = 0;
-        for (long t = t0; t < t1; t += tstep) {
-            if (!active(t)) continue;
-            mbar_wait(smem_u32(full_bar + s), ph);
-            fence_proxy_async();                      // cp.async wrote the images through the generic proxy
-            tc_fence_after();
-            const uint32_t a_base = base + (uint32_t)s * stage_bytes;
-            const uint32_t b_base = a_base + (uint32_t)p.ci_chunks_p * BWT_CHUNK_BYTES;
-            for (int mb = 0; mb < m_blocks; ++mb) {
+        BwtTileIter it{p.tile_mask, t0, t0, t1, tstep, 0u, k >> 5, k & 31};
+        for (long t = it.next(lane); t >= 0; t = it.next(lane)) {
+            if (lane == 0) {
+                mbar_wait(smem_u32(full_bar + s), ph);
+                fence_proxy_async();                      // cp.async wrote the images through the generic proxy
+                tc_fence_after();
+                const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+                const uint32_t b_base = a_base + (uint32_t)p.ci_chunks_p * BWT_CHUNK_BYTES;
+                for (int mb = 0; mb < m_blocks; ++mb) {
 #pragma unroll
-                for (int kk = 0; kk < BWT_ROWS / 16; ++kk) {             // 16 rows (two 8-row groups = 2048 bytes) per instruction
-                    const uint64_t adesc = umma_desc_mn_sw128(a_base + (uint32_t)(2 * mb) * BWT_CHUNK_BYTES + kk * 2048, BWT_CHUNK_BYTES);
-                    const uint64_t bdesc = umma_desc_mn_sw128(b_base + kk * 2048, BWT_CHUNK_BYTES);
-                    umma_bf16(tmem_d + (uint32_t)(mb * p.n_mma), adesc, bdesc, idesc, (started | (uint32_t)kk) ? 1u : 0u);
+                    for (int kk = 0; kk < BWT_ROWS / 16; ++kk) {             // 16 rows (two 8-row groups = 2048 bytes) per instruction
+                        const uint64_t adesc = umma_desc_mn_sw128(a_base + (uint32_t)(2 * mb) * BWT_CHUNK_BYTES + kk * 2048, BWT_CHUNK_BYTES);
+                        const uint64_t bdesc = umma_desc_mn_sw128(b_base + kk * 2048, BWT_CHUNK_BYTES);
+                        umma_bf16(tmem_d + (uint32_t)(mb * p.n_mma), adesc, bdesc, idesc, (started | (uint32_t)kk) ? 1u : 0u);
+                    }
                 }
+                umma_commit(smem_u32(empty_bar + s));
             }
             started = 1u;
-            umma_commit(smem_u32(empty_bar + s));
             if (++s == p.stages) { s = 0; ph ^= 1u; }
+            __syncwarp();
         }
-        if (started) umma_commit(smem_u32(accum_bar));
-        *reinterpret_cast<volatile uint32_t *>(tmem_slot + 1) = started;       // read by the epilogue after the barrier below
+        if (lane == 0) {
+            if (started) umma_commit(smem_u32(accum_bar));
+            *reinterpret_cast<volatile uint32_t *>(tmem_slot + 1) = started;       // read by the epilogue after the barrier below
+        }
     }
     __syncwarp();
     __syncthreads();
