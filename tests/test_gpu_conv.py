@@ -441,3 +441,33 @@ def test_weight_gradient_on_tensor_cores(pkg, dev, cin, cout, ksize, stride, tra
         finally:
             so.set_conv_mode(prev)
     assert rel_l2(grads["auto"][0], grads["f32"][0]) < 1.5e-2 and rel_l2(grads["auto"][1], grads["f32"][1]) < 1.5e-2
+
+
+@pytest.mark.parametrize("cin,cout", [(32, 16), (16, 1), (64, 1), (128, 16)])
+def test_weight_gradient_offsets_inner_variant(pkg, dev, cin, cout, monkeypatch):
+    """k_conv_bwd_weight_tc_kin (narrow outputs on large candidate sets: offsets inner, the G tile gathered once per tile, one TMEM
+    accumulator per offset), forced on a small input: bit-exact against the fp32 kernel on integer operands and bit-identical to the
+    offsets-outer tensor-core kernel's result up to the summation grouping (compared through the fp32 kernel on integers)."""
+    so = pkg.sparse_ops
+    ag = importlib.import_module(pkg.__name__ + ".autograd")
+    lib = pkg._lib.load()
+    L = importlib.import_module(pkg.__name__ + "._lib")
+    C, cs = setup(dev, pkg, seed=cin + cout, scale=2)
+    K = 27
+    nbr, tmask = cs.kernel_map(cs, 3, False)
+    rng = np.random.default_rng(cin * 3 + cout)
+    Fd = torch.from_numpy(rng.integers(-3, 4, (cs.n, cin)).astype(np.float32)).to(dev)
+    Gd = torch.from_numpy(rng.integers(-2, 3, (cs.n, cout)).astype(np.float32)).to(dev)
+    ref = torch.empty((K, cin, cout), device=dev)
+    L.call("pcg_conv_bwd_weight_f32", L.ptr(Fd), cin, L.ptr(nbr), nbr.shape[1], L.ptr(tmask), K, cs.n, L.ptr(Gd), cout, L.ptr(ref), L.stream())
+    fb, gb = ag._bf16_rows64(Fd), ag._bf16_rows64(Gd)
+    monkeypatch.setenv("PCG_BWT_KIN_MIN_TILES", "1")
+    ws = torch.empty(lib.pcg_conv_bwd_weight_tc_scratch_bytes(K, cin, cout, cs.n), dtype=torch.uint8, device=dev)
+    outs = []
+    for _ in range(2):
+        dw = torch.full((K, cin, cout), float("nan"), device=dev)
+        L.call("pcg_conv_bwd_weight_tc", L.ptr(fb), cin, L.ptr(gb), cout, L.ptr(nbr), nbr.shape[1], L.ptr(tmask), K, cs.n, L.ptr(ws), ws.numel(), L.ptr(dw), L.stream())
+        outs.append(dw)
+    torch.cuda.synchronize()
+    assert ws.numel() >= 148 * K * cin * cout * 4            # the offsets-inner variant was selected (one slice per SM)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], ref), f"max |d| = {float((outs[0] - ref).abs().max())}"

@@ -4,6 +4,8 @@
 // ascending order (fixed summation order, no atomics); tiles whose mask bit k is clear are skipped, which removes the
 // empty (tile, offset) combinations of strided and generative maps.  The input gradient needs no kernel of its own:
 // it is the forward convolution of G over the inverse map with W[k]^T (autograd.py).
+#include <stdlib.h>
+
 #include "pcg_common.cuh"
 
 #define BW_ROWS 128
@@ -315,6 +317,171 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------- narrow outputs: offsets inner, G loaded once per tile
+// For cout <= 16 and K <= 32 (the occupancy-head layers on the candidate sets: 88 k tiles x 27 dense offsets in the training batch)
+// the kernel above streams the padded F and G copies 27 times each and is HBM bound by its own padding.  Here a CTA owns a slice of
+// TILES and walks the offsets inside: the G tile is gathered once per tile, the F tiles of the 27 offsets of one tile are
+// neighbouring rows (L2 hits), and every offset has its own accumulator (TMEM columns 16 k .. 16 k + 15, 432 of 512 columns).
+// Same summation order per element: tiles ascending inside a slice, slices added in ascending order.
+#define BWK_STAGES 4
+__global__ void __launch_bounds__(160) k_conv_bwd_weight_tc_kin(const BwtParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t *sm = smem_raw + (base - raw);
+    const uint32_t stage_bytes = (uint32_t)p.ci_chunks_p * BWT_CHUNK_BYTES;        // F chunk images of one (tile, offset)
+    const uint32_t g_base = base + BWK_STAGES * stage_bytes;                        // two G images (one 64-channel chunk each)
+    uint8_t *ctl = sm + (size_t)BWK_STAGES * stage_bytes + 2 * BWT_CHUNK_BYTES;
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(ctl);            // [BWK_STAGES]
+    uint64_t *empty_bar = full_bar + BWK_STAGES;                       // [BWK_STAGES]
+    uint64_t *gfull_bar = empty_bar + BWK_STAGES;                      // [2]
+    uint64_t *gempty_bar = gfull_bar + 2;                              // [2]
+    uint64_t *accum_bar = gempty_bar + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_bar + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long t0 = blockIdx.x, tstep = gridDim.x;
+    if (tid == 0) {
+        for (int s = 0; s < BWK_STAGES; ++s) {
+            mbar_init(smem_u32(full_bar + s), 32 * p.ci_chunks_p);
+            mbar_init(smem_u32(empty_bar + s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(smem_u32(gfull_bar + s), 32);
+            mbar_init(smem_u32(gempty_bar + s), 1);
+        }
+        mbar_init(smem_u32(accum_bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_d = *tmem_slot;
+    const int row_f = p.ci_chunks * 128, row_g = p.co_chunks * 128;
+    const int m_blocks = p.ci_chunks_p / 2;                            // 1 (cin <= 128)
+
+    if (warp < 3) {
+        // ------------------------------------------------------------------ F producers: warp w gathers the (tile, offset) items w, w + 3, ...
+        const uint8_t *fsrc = p.feats + (lane & 7) * 16;
+        long item = 0;                                                  // running index over the active (tile, offset) pairs of this CTA
+        for (long t = t0; t < p.tiles; t += tstep) {
+            uint32_t m = __ldg(p.tile_mask + t * 4);                   // K <= 32: one mask word
+            while (m) {
+                const int k = __ffs(m) - 1;
+                m &= m - 1;
+                if (item % 3 == warp) {
+                    int idx[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) idx[u] = __ldg(p.nbr + (long)k * p.pitch + t * BWT_ROWS + lane + 32 * u);
+                    const int s = (int)(item % BWK_STAGES);
+                    const uint32_t par = (uint32_t)((item / BWK_STAGES) & 1);
+                    mbar_wait(smem_u32(empty_bar + s), par ^ 1u);
+                    const uint32_t fb = smem_u32(full_bar + s);
+                    for (int c = 0; c < p.ci_chunks_p; ++c) {
+                        const uint32_t dst = base + (uint32_t)s * stage_bytes + (uint32_t)c * BWT_CHUNK_BYTES;
+                        if (c < p.ci_chunks) tc_lsu_gather_tile<128, false>(dst, fsrc + c * 128, row_f, idx, lane);
+                        else {
+                            const int none[4] = {-1, -1, -1, -1};
+                            tc_lsu_gather_tile<128, false>(dst, fsrc, row_f, none, lane);
+                        }
+                        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
+                    }
+                }
+                ++item;
+            }
+        }
+    } else if (warp == 3) {
+        // ------------------------------------------------------------------ G producer: one image per tile, double buffered
+        const uint8_t *gsrc = p.gout + (lane & 7) * 16;
+        long n = 0;
+        for (long t = t0; t < p.tiles; t += tstep) {
+            if (__ldg(p.tile_mask + t * 4) == 0u) continue;
+            int idx[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long o = t * BWT_ROWS + lane + 32 * u;
+                idx[u] = o < p.n_out ? (int)o : -1;
+            }
+            const int s = (int)(n & 1);
+            mbar_wait(smem_u32(gempty_bar + s), (uint32_t)((n >> 1) & 1) ^ 1u);
+            tc_lsu_gather_tile<128, false>(g_base + (uint32_t)s * BWT_CHUNK_BYTES, gsrc, row_g, idx, lane);
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(gfull_bar + s)) : "memory");
+            ++n;
+        }
+    } else {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(16 >> 3) << 17) | ((128u >> 4) << 24);
+            long item = 0, n = 0;
+            uint32_t started = 0;                                       // bit k: accumulator k holds a value
+            for (long t = t0; t < p.tiles; t += tstep) {
+                uint32_t m = __ldg(p.tile_mask + t * 4);
+                if (m == 0u) continue;
+                const int gs = (int)(n & 1);
+                mbar_wait(smem_u32(gfull_bar + gs), (uint32_t)((n >> 1) & 1));
+                while (m) {
+                    const int k = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int s = (int)(item % BWK_STAGES);
+                    mbar_wait(smem_u32(full_bar + s), (uint32_t)((item / BWK_STAGES) & 1));
+                    fence_proxy_async();
+                    tc_fence_after();
+                    const uint32_t a_base = base + (uint32_t)s * stage_bytes;
+#pragma unroll
+                    for (int kk = 0; kk < BWT_ROWS / 16; ++kk) {
+                        const uint64_t adesc = umma_desc_mn_sw128(a_base + kk * 2048, BWT_CHUNK_BYTES);
+                        const uint64_t bdesc = umma_desc_mn_sw128(g_base + (uint32_t)gs * BWT_CHUNK_BYTES + kk * 2048, BWT_CHUNK_BYTES);
+                        umma_bf16(tmem_d + (uint32_t)(k * 16), adesc, bdesc, idesc, (((started >> k) & 1u) | (uint32_t)kk) ? 1u : 0u);
+                    }
+                    started |= 1u << k;
+                    umma_commit(smem_u32(empty_bar + s));
+                    ++item;
+                }
+                umma_commit(smem_u32(gempty_bar + gs));
+                ++n;
+            }
+            if (started) umma_commit(smem_u32(accum_bar));
+            tmem_slot[1] = started;
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    const uint32_t started = *reinterpret_cast<volatile uint32_t *>(tmem_slot + 1);
+    if (warp < 4) {
+        if (started) {
+            mbar_wait(smem_u32(accum_bar), 0);
+            tc_fence_after();
+        }
+        float *dst = p.partial + (size_t)blockIdx.x * p.K * (size_t)p.cin * p.cout;
+        const int ci = tid;                                              // TMEM lane = input channel (m_blocks == 1)
+        const uint32_t lane_base = tmem_d + ((uint32_t)(warp * 32) << 16);
+        for (int k = 0; k < p.K; ++k) {
+            uint32_t v[16];
+            if ((started >> k) & 1u) tmem_ld16(lane_base + (uint32_t)(k * 16), v);      // warp-uniform
+            else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = 0u;
+            }
+            if (ci < p.cin) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (j < p.cout) dst[((size_t)k * p.cin + ci) * p.cout + j] = __uint_as_float(v[j]);
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(512u) : "memory");
+    }
+    (void)m_blocks;
+}
+
 // dw[i] = sum_s partial[s][i], s ascending
 __global__ void k_bwd_reduce_partials(const float *__restrict__ partial, int slices, long n, float *__restrict__ dw) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -326,8 +493,14 @@ __global__ void k_bwd_reduce_partials(const float *__restrict__ partial, int sli
     }
 }
 
-static long bwt_slices(int K, long tiles) {
-    long s = cdiv(2L * PCG_SMS, K);          // about two waves of CTAs (one CTA per SM: the operand ring takes most of the shared memory)
+static bool bwt_k_inner(int K, int cin, int cout, long tiles) {      // narrow outputs on many tiles: k_conv_bwd_weight_tc_kin
+    const char *e = getenv("PCG_BWT_KIN_MIN_TILES");          // tests force the variant on small inputs
+    return cout <= 16 && K <= 32 && cin <= 128 && tiles >= (e ? atol(e) : 4L * PCG_SMS);
+}
+
+static long bwt_slices(int K, int cin, int cout, long tiles) {
+    if (bwt_k_inner(K, cin, cout, tiles)) return PCG_SMS;      // one CTA per SM, each a strided slice of the tiles
+    long s = (2L * PCG_SMS) / K;             // at most two full waves of CTAs (one CTA per SM: the operand ring takes most of the shared memory)
     if (s > tiles) s = tiles;
     if (s > 64) s = 64;
     return s < 1 ? 1 : s;
@@ -335,7 +508,7 @@ static long bwt_slices(int K, long tiles) {
 
 extern "C" size_t pcg_conv_bwd_weight_tc_scratch_bytes(int K, int cin, int cout, long n_out) {
     const long tiles = cdiv(n_out > 0 ? n_out : 1, BWT_ROWS);
-    return (size_t)bwt_slices(K, tiles) * K * cin * cout * sizeof(float) + 256;
+    return (size_t)bwt_slices(K, cin, cout, tiles) * K * cin * cout * sizeof(float) + 256;
 }
 
 extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const void *gout_bf16, int cout, const int32_t *nbr, long nbr_pitch,
@@ -355,7 +528,7 @@ extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const voi
     p.feats = reinterpret_cast<const uint8_t *>(feats_bf16); p.gout = reinterpret_cast<const uint8_t *>(gout_bf16);
     p.nbr = nbr; p.tile_mask = tile_mask; p.pitch = nbr_pitch; p.n_out = n_out;
     p.tiles = cdiv(n_out, BWT_ROWS);
-    const long slices = bwt_slices(K, p.tiles);
+    const long slices = bwt_slices(K, cin, cout, p.tiles);
     p.tiles_per_slice = cdiv(p.tiles, slices);
     p.cin = cin; p.cout = cout; p.K = K;
     p.ci_chunks = (cin + 63) / 64; p.ci_chunks_p = (p.ci_chunks + 1) & ~1; p.co_chunks = (cout + 63) / 64;
@@ -371,6 +544,17 @@ extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const voi
     p.stages = stages;
     PCG_CHECK_ARG(scratch && scratch_bytes >= (size_t)slices * n_w * sizeof(float), "pcg_conv_bwd_weight_tc: scratch too small");
     p.partial = reinterpret_cast<float *>(scratch);
+    if (bwt_k_inner(K, cin, cout, p.tiles)) {
+        const size_t smem_k = 1024 + (size_t)BWK_STAGES * p.ci_chunks_p * BWT_CHUNK_BYTES + 2 * BWT_CHUNK_BYTES + 256;
+        PCG_CUDA(cudaFuncSetAttribute(k_conv_bwd_weight_tc_kin, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_k));
+        k_conv_bwd_weight_tc_kin<<<(unsigned)slices, 160, smem_k, st>>>(p);
+        PCG_LAUNCHED();
+        long blocks_k = cdiv(n_w, 256);
+        if (blocks_k > PCG_SMS * 8) blocks_k = PCG_SMS * 8;
+        k_bwd_reduce_partials<<<(unsigned)blocks_k, 256, 0, st>>>(p.partial, (int)slices, n_w, dweight);
+        PCG_LAUNCHED();
+        return 0;
+    }
     const size_t smem = 1024 + (size_t)stages * stage_bytes + 256;
     PCG_CUDA(cudaFuncSetAttribute(k_conv_bwd_weight_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_conv_bwd_weight_tc<<<dim3((unsigned)K, (unsigned)slices), 160, smem, st>>>(p);
