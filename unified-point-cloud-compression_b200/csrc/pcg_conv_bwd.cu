@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
 
     if (tid == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            mbar_init(smem_u32(full_bar + s), 32 * n_chunks);      // one cp.async-completion arrive per lane and chunk image
+            mbar_init(smem_u32(full_bar + s), 32 * (n_chunks - (p.ci_chunks_p - p.ci_chunks)));      // one cp.async-completion arrive per lane and GATHERED chunk image
             mbar_init(smem_u32(empty_bar + s), 1);
         }
         mbar_init(smem_u32(accum_bar), 1);
@@ -202,6 +202,12 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // the zero padding chunk of the last 128-channel block (cin <= 64, 129..192) never changes: written once per stage here
+    for (int s = 0; s < p.stages; ++s)
+        for (int c = p.ci_chunks; c < p.ci_chunks_p; ++c)
+            for (uint32_t off = tid * 16u; off < BWT_CHUNK_BYTES; off += 160u * 16u)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(base + (uint32_t)s * stage_bytes + (uint32_t)c * BWT_CHUNK_BYTES + off), "r"(0u) : "memory");
+    fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -237,10 +243,8 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc(const BwtParams p) {
             for (int c = warp; c < n_chunks; c += 4) {
                 const uint32_t dst = st_base + (uint32_t)c * BWT_CHUNK_BYTES;
                 if (c < p.ci_chunks) tc_lsu_gather_tile<128, false>(dst, fsrc + c * 128, row_f, idx_f, lane);
-                else if (c < p.ci_chunks_p) {                                   // zero padding chunk of the last 128-channel block
-                    const int none[4] = {-1, -1, -1, -1};
-                    tc_lsu_gather_tile<128, false>(dst, fsrc, row_f, none, lane);
-                } else tc_lsu_gather_tile<128, false>(dst, gsrc + (c - p.ci_chunks_p) * 128, row_g, idx_g, lane);
+                else if (c < p.ci_chunks_p) continue;                          // the padding chunk stays zero
+                else tc_lsu_gather_tile<128, false>(dst, gsrc + (c - p.ci_chunks_p) * 128, row_g, idx_g, lane);
                 asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
             }
             if (++s == p.stages) { s = 0; ++wrap; }
@@ -343,7 +347,7 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc_kin(const BwtParams 
     const long t0 = blockIdx.x, tstep = gridDim.x;
     if (tid == 0) {
         for (int s = 0; s < BWK_STAGES; ++s) {
-            mbar_init(smem_u32(full_bar + s), 32 * p.ci_chunks_p);
+            mbar_init(smem_u32(full_bar + s), 32 * p.ci_chunks);
             mbar_init(smem_u32(empty_bar + s), 1);
         }
         for (int s = 0; s < 2; ++s) {
@@ -357,6 +361,11 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc_kin(const BwtParams 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    for (int s = 0; s < BWK_STAGES; ++s)                              // the zero padding chunk (cin <= 64): written once
+        for (int c = p.ci_chunks; c < p.ci_chunks_p; ++c)
+            for (uint32_t off = tid * 16u; off < BWT_CHUNK_BYTES; off += 160u * 16u)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(base + (uint32_t)s * stage_bytes + (uint32_t)c * BWT_CHUNK_BYTES + off), "r"(0u) : "memory");
+    fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -381,13 +390,9 @@ __global__ void __launch_bounds__(160) k_conv_bwd_weight_tc_kin(const BwtParams 
                     const uint32_t par = (uint32_t)((item / BWK_STAGES) & 1);
                     mbar_wait(smem_u32(empty_bar + s), par ^ 1u);
                     const uint32_t fb = smem_u32(full_bar + s);
-                    for (int c = 0; c < p.ci_chunks_p; ++c) {
+                    for (int c = 0; c < p.ci_chunks; ++c) {          // (the padding chunk stays zero)
                         const uint32_t dst = base + (uint32_t)s * stage_bytes + (uint32_t)c * BWT_CHUNK_BYTES;
-                        if (c < p.ci_chunks) tc_lsu_gather_tile<128, false>(dst, fsrc + c * 128, row_f, idx, lane);
-                        else {
-                            const int none[4] = {-1, -1, -1, -1};
-                            tc_lsu_gather_tile<128, false>(dst, fsrc, row_f, none, lane);
-                        }
+                        tc_lsu_gather_tile<128, false>(dst, fsrc + c * 128, row_f, idx, lane);
                         asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(fb) : "memory");
                     }
                 }
