@@ -330,6 +330,21 @@ def main():
         t_res1 = timed(step_resident, min(args.steps, 5), use_pipe=False) / min(args.steps, 5) if pipe is not None else None
         t_e2e1 = timed(step_e2e, min(args.steps, 5), use_pipe=False) / min(args.steps, 5) if pipe is not None else None
         barrier()
+        # compress() / decompress() as the reference defines them (model/model.py:94-250, component form): the host range coder and
+        # its device<->host copies INSIDE the timed region, one frame at a time (reported beside the metric, which excludes them)
+        hc_ms = None
+        if rank == 0:
+            reps = []
+            for i in range(4):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                bits, shapes, ks, coords_, qv = net.compress(dev_clouds[0], q, block_size=1024)
+                rec_ = net.decompress(coordinates=coords_, strings=bits, shape=shapes, k=ks, q_vals=qv)
+                torch.cuda.synchronize()
+                if i:
+                    reps.append(1e3 * (time.perf_counter() - t0))
+            hc_ms = sum(reps) / len(reps)
+            hc_bytes = sum(len(s_[0]) for blk in bits for s_ in blk)
         # roofline pass: the same step with per-launch CUDA events around every convolution kernel
         so.profiler = so.ConvProfiler()
         step_resident()
@@ -433,6 +448,11 @@ def main():
             "e2e": {"value": total_points / (ms_e2e * 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": sum(v[0] for v in io_frame.values()), "d2h_bytes_per_step": sum(v[1] for v in io_frame.values())},
             "gpu_launches": int(launches), "roofline": roofline}
+    if hc_ms is not None:
+        n0 = len(frames[0][0])
+        line["with_host_coder"] = {"note": "UnifiedModel.compress + decompress, component form, host rANS coder and its copies included, one frame at a time",
+                                   "ms_per_frame": hc_ms, "value": n0 / (hc_ms * 1e3), "unit": UNIT, "payload_bytes": hc_bytes,
+                                   "bits_per_point": 8.0 * hc_bytes / n0}
     if t_res1 is not None:
         n1 = len(frames[0][0])
         line["single_stream"] = {"note": "one frame at a time on one stream, rank 0", "ms_per_frame": t_res1, "value": n1 / (t_res1 * 1e3),
