@@ -199,9 +199,21 @@ def main():
     if world > 1 and os.environ.get("PCG_PIN", "1") == "1":
         # one slice of the host cores per rank: every rank runs a launching thread per frame in flight, and 8 ranks x 3 threads
         # migrating over 16 cores cost ~6 % of the 8-GPU throughput in round 1 (host enqueue is 80 % of a step's wall time)
-        cores = sorted(os.sched_getaffinity(0))
-        per = max(1, len(cores) // world)
-        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        # (whole PHYSICAL cores: hyper-thread siblings stay together, so no two ranks share a core's execution units)
+        cpus = sorted(os.sched_getaffinity(0))
+        groups = {}
+        for c in cpus:
+            try:
+                sib = open(f"/sys/devices/system/cpu/cpu{c}/topology/thread_siblings_list").read().strip()
+            except OSError:
+                sib = str(c)
+            groups.setdefault(sib, []).append(c)
+        phys = [g for _, g in sorted(groups.items(), key=lambda kv: min(kv[1]))]
+        if len(phys) >= world:
+            mine = [c for g in phys[local_rank::world] for c in g]
+        else:
+            per = max(1, len(cpus) // world)
+            mine = cpus[local_rank * per:(local_rank + 1) * per] or cpus
         os.sched_setaffinity(0, set(mine))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
