@@ -172,18 +172,38 @@ __global__ void __launch_bounds__(128) k_cells_kernel_map3(const uint64_t *__res
     int Cx = pcg_floor_to(c.y, ts_in), Cy = pcg_floor_to(c.z, ts_in), Cz = pcg_floor_to(c.w, ts_in);
     int bx = (c.y - Cx) / ts_out, by = (c.z - Cy) / ts_out, bz = (c.w - Cz) / ts_out;
     int own = live ? __ldg(out_cell + o) : -1;
+    // the 7 neighbour-cell probes of a child are independent: their probe chains advance in lockstep, so the (dependent) loads of
+    // one chain overlap those of the others instead of running one chain after the other (the kernel is latency bound)
+    int cellv[8];
+    uint64_t key[8], slot[8];
+    uint32_t pend = 0;
+    cellv[0] = own;
+#pragma unroll
+    for (int s = 1; s < 8; ++s) {
+        cellv[s] = -1;
+        const int x = Cx + ((s & 1) ? (bx ? ts_in : -ts_in) : 0);
+        const int y = Cy + ((s & 2) ? (by ? ts_in : -ts_in) : 0);
+        const int z = Cz + ((s & 4) ? (bz ? ts_in : -ts_in) : 0);
+        key[s] = pcg_pack(c.x, x, y, z);
+        slot[s] = pcg_mix(key[s]) & cmask;
+        if (live && pcg_in_range(c.x, x, y, z)) pend |= 1u << s;
+    }
+    while (pend) {
+        uint64_t got[8];
+#pragma unroll
+        for (int s = 1; s < 8; ++s)
+            if ((pend >> s) & 1u) got[s] = __ldg(cell_keys + slot[s]);
+#pragma unroll
+        for (int s = 1; s < 8; ++s) {
+            if (!((pend >> s) & 1u)) continue;
+            if (got[s] == key[s]) { cellv[s] = __ldg(cell_vals + slot[s]); pend &= ~(1u << s); }
+            else if (got[s] == PCG_EMPTY_KEY) pend &= ~(1u << s);
+            else slot[s] = (slot[s] + 1) & cmask;
+        }
+    }
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
-        int cell = -1;
-        if (live) {
-            if (s == 0) cell = own;
-            else {
-                int x = Cx + ((s & 1) ? (bx ? ts_in : -ts_in) : 0);
-                int y = Cy + ((s & 2) ? (by ? ts_in : -ts_in) : 0);
-                int z = Cz + ((s & 4) ? (bz ? ts_in : -ts_in) : 0);
-                if (pcg_in_range(c.x, x, y, z)) cell = pcg_table_find(cell_keys, cell_vals, cmask, pcg_pack(c.x, x, y, z));
-            }
-        }
+        const int cell = cellv[s];
         s_base[s][tid] = cell >= 0 ? __ldg(cell_base + cell) : 0;
         s_mask[s][tid] = cell >= 0 ? cell_mask[cell] : (uint8_t)0;
     }
