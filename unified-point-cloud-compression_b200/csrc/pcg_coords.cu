@@ -140,6 +140,13 @@ struct FlagFirstStrided {
     const uint64_t *keys;
     const int32_t *vals;
     uint64_t mask;
+    using probe_tag = int;                            // probes advanced in lockstep by the compaction kernel (pcg_compact.cuh)
+    __device__ bool key_of(long i, uint64_t &key) const {
+        int4 c = sk.coord(i);
+        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
+        key = pcg_pack(c.x, c.y, c.z, c.w);
+        return true;
+    }
     __device__ bool operator()(long i) const {
         int4 c = sk.coord(i);
         if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
@@ -282,6 +289,13 @@ struct FlagFirstGen {
     const uint64_t *keys;
     const int32_t *vals;
     uint64_t mask;
+    using probe_tag = int;
+    __device__ bool key_of(long i, uint64_t &key) const {
+        int4 c = gk.coord(i);
+        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
+        key = pcg_pack(c.x, c.y, c.z, c.w);
+        return true;
+    }
     __device__ bool operator()(long i) const {
         int4 c = gk.coord(i);
         if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
@@ -356,50 +370,20 @@ __global__ void __launch_bounds__(128 * KM_SLICES_MAX) k_kernel_map(const uint64
     __syncthreads();
     const int lo = (ksize & 1) ? -(ksize >> 1) : 0;
     const int k2 = ksize * ksize;
-    // four offsets per step, their probe chains advanced in lockstep: the dependent loads of one chain overlap those of the others
-    // (an offset loop with one data-dependent probe loop per iteration serialises them; the kernel is latency bound)
-    for (int k0 = threadIdx.y; k0 < K; k0 += 4 * blockDim.y) {
-        uint64_t key[4], slot[4];
-        int row[4];
-        uint32_t pend = 0;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int k = k0 + u * blockDim.y;
-            row[u] = -1;
-            if (k >= K || !live) continue;
-            const int iz = k / k2, iy = (k - iz * k2) / ksize, ix = k - iz * k2 - iy * ksize;
-            const int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
+    for (int k = threadIdx.y; k < K; k += blockDim.y) {
+        const int iz = k / k2, iy = (k - iz * k2) / ksize, ix = k - iz * k2 - iy * ksize;
+        int row = -1;
+        if (live) {
+            int x = c.y + (lo + ix) * step, y = c.z + (lo + iy) * step, z = c.w + (lo + iz) * step;
             // lattice > 0: input rows only exist on multiples of `lattice` (transposed conv onto a finer
             // grid), so most offsets cannot hit for a given output parity -- no probe needed
-            const bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
-            if (possible && pcg_in_range(c.x, x, y, z)) {
-                key[u] = pcg_pack(c.x, x, y, z);
-                slot[u] = pcg_mix(key[u]) & mask;
-                pend |= 1u << u;
-            }
+            bool possible = lattice <= 1 || ((x % lattice) == 0 && (y % lattice) == 0 && (z % lattice) == 0);
+            if (possible && pcg_in_range(c.x, x, y, z)) row = pcg_table_find(keys, vals, mask, pcg_pack(c.x, x, y, z));
         }
-        while (pend) {
-            uint64_t got[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if ((pend >> u) & 1u) got[u] = __ldg(keys + slot[u]);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!((pend >> u) & 1u)) continue;
-                if (got[u] == key[u]) { row[u] = __ldg(vals + slot[u]); pend &= ~(1u << u); }
-                else if (got[u] == PCG_EMPTY_KEY) pend &= ~(1u << u);
-                else slot[u] = (slot[u] + 1) & mask;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int k = k0 + u * blockDim.y;
-            if (k >= K) continue;                     // uniform over the warp (k depends on threadIdx.y only)
-            nbr[(long)k * pitch + o] = row[u];        // rows past n_out are the -1 padding of the last tile
-            if (tile_mask) {
-                unsigned any = __ballot_sync(0xffffffffu, row[u] >= 0);
-                if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
-            }
+        nbr[(long)k * pitch + o] = row;      // rows past n_out are the -1 padding of the last tile
+        if (tile_mask) {
+            unsigned any = __ballot_sync(0xffffffffu, row >= 0);
+            if (any && (threadIdx.x & 31) == 0) atomicOr(&smask[k >> 5], 1u << (k & 31));
         }
     }
     if (tile_mask) {
