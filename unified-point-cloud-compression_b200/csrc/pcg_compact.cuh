@@ -106,14 +106,6 @@ __global__ void __launch_bounds__(PCG_CHUNK_THREADS) pcg_k_scatter(long n, const
 #define PCG_TILE_AGGREGATE 1ull
 #define PCG_TILE_INCLUSIVE 2ull
 
-// A flag functor of the form "the table maps my key to ME" (first-occurrence tests of the strided / generated set builders) may
-// expose `probe_tag`, `bool key_of(long i, uint64_t &key) const` and the table (`keys`, `vals`, `mask`): its PCG_CHUNK_ITEMS probes
-// per thread are then advanced in lockstep (independent chains overlap) instead of one after the other.
-template <class T, class = void>
-struct pcg_has_probe { static constexpr bool value = false; };
-template <class T>
-struct pcg_has_probe<T, decltype((void)sizeof(typename T::probe_tag))> { static constexpr bool value = true; };
-
 template <class FlagFn, class EmitFn>
 __global__ void __launch_bounds__(PCG_CHUNK_THREADS) pcg_k_compact_single(long n, FlagFn flag, EmitFn emit, unsigned long long *tile_state,
                                                                          int32_t *ticket, int32_t *d_n_out, int n_tiles) {
@@ -124,38 +116,10 @@ __global__ void __launch_bounds__(PCG_CHUNK_THREADS) pcg_k_compact_single(long n
     const long first = (long)tile * PCG_CHUNK + (long)threadIdx.x * PCG_CHUNK_ITEMS;
     bool f[PCG_CHUNK_ITEMS];
     int cnt = 0;
-    if constexpr (pcg_has_probe<FlagFn>::value) {
-        uint64_t key[PCG_CHUNK_ITEMS], slot[PCG_CHUNK_ITEMS];
-        uint32_t pend = 0;
 #pragma unroll
-        for (int j = 0; j < PCG_CHUNK_ITEMS; ++j) {
-            f[j] = false;
-            if (first + j < n && flag.key_of(first + j, key[j])) {
-                slot[j] = pcg_mix(key[j]) & flag.mask;
-                pend |= 1u << j;
-            }
-        }
-        while (pend) {
-            uint64_t got[PCG_CHUNK_ITEMS];
-#pragma unroll
-            for (int j = 0; j < PCG_CHUNK_ITEMS; ++j)
-                if ((pend >> j) & 1u) got[j] = __ldg(flag.keys + slot[j]);
-#pragma unroll
-            for (int j = 0; j < PCG_CHUNK_ITEMS; ++j) {
-                if (!((pend >> j) & 1u)) continue;
-                if (got[j] == key[j]) { f[j] = __ldg(flag.vals + slot[j]) == (int)(first + j); pend &= ~(1u << j); }
-                else if (got[j] == PCG_EMPTY_KEY) pend &= ~(1u << j);
-                else slot[j] = (slot[j] + 1) & flag.mask;
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < PCG_CHUNK_ITEMS; ++j) cnt += f[j] ? 1 : 0;
-    } else {
-#pragma unroll
-        for (int j = 0; j < PCG_CHUNK_ITEMS; ++j) {
-            f[j] = first + j < n && flag(first + j);
-            cnt += f[j] ? 1 : 0;
-        }
+    for (int j = 0; j < PCG_CHUNK_ITEMS; ++j) {
+        f[j] = first + j < n && flag(first + j);
+        cnt += f[j] ? 1 : 0;
     }
     int total;
     const int excl = pcg_block_excl_scan(cnt, total);

@@ -140,13 +140,6 @@ struct FlagFirstStrided {
     const uint64_t *keys;
     const int32_t *vals;
     uint64_t mask;
-    using probe_tag = int;                            // probes advanced in lockstep by the compaction kernel (pcg_compact.cuh)
-    __device__ bool key_of(long i, uint64_t &key) const {
-        int4 c = sk.coord(i);
-        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
-        key = pcg_pack(c.x, c.y, c.z, c.w);
-        return true;
-    }
     __device__ bool operator()(long i) const {
         int4 c = sk.coord(i);
         if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
@@ -289,13 +282,6 @@ struct FlagFirstGen {
     const uint64_t *keys;
     const int32_t *vals;
     uint64_t mask;
-    using probe_tag = int;
-    __device__ bool key_of(long i, uint64_t &key) const {
-        int4 c = gk.coord(i);
-        if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
-        key = pcg_pack(c.x, c.y, c.z, c.w);
-        return true;
-    }
     __device__ bool operator()(long i) const {
         int4 c = gk.coord(i);
         if (!pcg_in_range(c.x, c.y, c.z, c.w)) return false;
