@@ -267,6 +267,9 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
     if (unit >= n_units) return;                    // warp-uniform
     const int part = lane % LANES;
     const long t_row = (long)125 * cout;
+    float bv[8];                                   // this lane's 8 bias values, loaded once (a lane's channels never change)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bv[j] = bias ? __ldg(bias + part * 8 + j) : 0.f;
     // Grid-stride over units with the NEXT unit's parent row / child mask / row base requested before the current unit's rows
     // of T: each unit is a chain of two dependent global loads (parent list -> T rows) with few bytes in flight per warp, so the
     // first link of unit i+1 overlaps the second link of unit i.
@@ -322,7 +325,7 @@ __global__ void __launch_bounds__(256) k_cells_reduce(const __nv_bfloat16 *__res
             const long o = (long)cbase + __popc(cmask & ((1u << b) - 1u));
             const int c0 = part * 8;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = pcg_apply_act(acc[j] + (bias ? __ldg(bias + c0 + j) : 0.f), act);
+            for (int j = 0; j < 8; ++j) acc[j] = pcg_apply_act(acc[j] + bv[j], act);
             if (out_f32) {
                 float4 *dst = reinterpret_cast<float4 *>(out_f32 + o * cout + c0);
                 dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
