@@ -150,6 +150,8 @@ def main():
                     help="frame10: BASELINE configs[1] (default, the metric's config); block128: configs[0]; stream11: configs[2], 64-frame 11-bit "
                          "stream sharded by frame (strong scaling); train256: configs[3], the training step on 256^3 blocks, batch 8 per GPU")
     ap.add_argument("--frames", type=int, default=64, help="stream11: frames in the sequence")
+    ap.add_argument("--frames-per-step", type=int, default=0, help="frame10 / block128 / frame11: distinct frames a step codes through the "
+                    "in-flight pipeline (default: 4 x --in-flight, or 1 for a single stream)")
     ap.add_argument("--serial-blocks", action="store_true", help="stream11: code the blocks of a frame one after the other (the reference's "
                     "loop, model.py:137-176) instead of as one batched sparse tensor")
     ap.add_argument("--topk-from", default="decoder", choices=["decoder", "encoder"],
@@ -171,8 +173,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": f"CVPR_inverse_scaling {args.workload}: {max(1, args.in_flight)} synthetic surface-sampled frame(s) per rank per step, "
-                          "compress+decompress, random-init weights, q=(0.5,0.5)",
+    fps = args.frames_per_step or (4 * max(1, args.in_flight) if args.in_flight > 1 else 1)
+    config = {"workload": f"CVPR_inverse_scaling {args.workload}: {fps} synthetic surface-sampled frame(s) per rank per step "
+                          f"({max(1, args.in_flight)} in flight), compress+decompress, random-init weights, q=(0.5,0.5)",
               "sharding": f"{world} rank(s), independent frames on each, no collective"}
 
     if args.impl == "reference":
@@ -237,8 +240,18 @@ def main():
     net.g_s.topk_from_encoder = args.topk_from == "encoder"
 
     depth = max(1, args.in_flight)
-    # a step codes `depth` frames (one per worker stream): frame seeds rank, rank + world, ...
-    frames = [make_frame(args.workload, seed=rank + j * world) for j in range(depth)]
+    # a step codes F distinct frames through the pipeline of `depth` worker streams: two generated frames (seeds rank, rank + world)
+    # and integer translations of them (different coordinates, hence different hash tables / maps / symbols, at no generation cost).
+    # With F = 4 x depth the frames of a step desynchronise like a real sequence does (one stream in its HBM-bound kernels while the
+    # other is in its tensor-core kernels) instead of starting in lockstep every step, and the step's inputs (F x 20 MB) exceed L2.
+    F = args.frames_per_step or (4 * depth if depth > 1 else 1)
+    bases = [make_frame(args.workload, seed=rank + j * world) for j in range(min(2, F))]
+    shift_rng = np.random.default_rng(1234 + rank)
+    frames = []
+    for j in range(F):
+        p, c = bases[j % len(bases)]
+        d = shift_rng.integers(0, 9, size=3) if j >= len(bases) else np.zeros(3, dtype=np.int64)
+        frames.append(((p + d).astype(p.dtype), c))
     n_points = sum(len(p) for p, _ in frames)
     host_clouds = [torch.from_numpy(np.concatenate([p.astype(np.float32), c], axis=1)).pin_memory() for p, c in frames]
     dev_clouds = [h.to(dev) for h in host_clouds]
@@ -298,7 +311,7 @@ def main():
             if pipe is None or not use_pipe:
                 fn()
             else:
-                pipe.map(fn, range(depth), after=e0)             # `depth` frames, one per worker stream; this stream waits for all
+                pipe.map(fn, range(F), after=e0)                 # F frames through `depth` worker streams; this stream waits for all
             host_ms.append(1e3 * (time.perf_counter() - t0))     # host enqueue time (includes the step's own syncs)
             e1.record()
             flush[:1].fill_(2)                               # 1-block marker launch: end of the step in an ncu launch list
@@ -310,13 +323,13 @@ def main():
         return total
 
     with torch.no_grad():
-        for _ in range(max(args.warmup, 3)):
-            for j in range(depth):
+        for w in range(max(args.warmup, 3)):
+            for j in range(F if w == 0 else min(F, 2)):
                 step_resident(j)
         barrier()
         if pipe is not None:                                     # warm the worker streams too (scratch, allocator pools)
             for _ in range(2):
-                pipe.map(step_resident, range(depth))
+                pipe.map(step_resident, range(F))
             barrier()
         # everything allocated so far (modules, torch, numpy) is long-lived: take it out of the collector's generations so that
         # a full collection cannot stall a timed step for ~100 ms (seen as a one-off 130 ms e2e step at N=2)
@@ -331,11 +344,11 @@ def main():
         launches = (pkg._lib.launch_count() - l0) // max(args.steps, 1)
         barrier()
         clk = clocks.stop() if clocks is not None else None
-        for _ in range(3):
-            for j in range(depth):
+        for w in range(3):
+            for j in range(F if w == 0 else min(F, 2)):
                 step_e2e(j)
         if pipe is not None:
-            pipe.map(step_e2e, range(depth))
+            pipe.map(step_e2e, range(F))
         barrier()
         t_e2e = timed(step_e2e, args.steps)
         # the same frame (slot 0) alone on one stream, for reference next to the frames-in-flight numbers
@@ -427,7 +440,7 @@ def main():
                 "peak_kind": peak_kind, "frac_of_burst_peak": achieved / pk["bf16_burst"], "frac_of_sustained_peak": achieved / pk["bf16_sustained"],
                 "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": pk["src"], "launches": tc_launches, "kernel_ms_per_step": tc_ms,
-                "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * depth / ms_res if ms_res else None,
+                "all_conv_ms_per_step": all_conv_ms, "share_of_step": tc_ms * F / ms_res if ms_res else None,
                 "per": "one frame (the roofline pass codes a single frame on one stream)",
                 "algorithmic_gflop_per_step": tc_flops / 1e9,
                 "by_shape": {"conv_tc": shapes("conv_tc"), "gemm_first": shapes("gemm_first")},
@@ -452,9 +465,9 @@ def main():
     line = {"metric": METRIC, "value": total_points / (ms_res * 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16" if args.conv_mode == "auto" else "f32", "data": "synthetic",
-            "config": dict(config, points_per_step=n_points, frames_per_step=depth,
+            "config": dict(config, points_per_step=n_points, frames_per_step=F,
                            in_flight=f"{depth} frame(s) in flight per GPU: {depth} host thread(s) x CUDA stream(s) (codec.FramePipeline)",
-                           l2="512 MiB flush buffer written between timed steps", conv_mode=args.conv_mode,
+                           l2=f"512 MiB flush buffer written between timed steps; a step's inputs ({F} frames) are larger than L2 as well", conv_mode=args.conv_mode,
                            topk_from=args.topk_from + (" (measurement switch: every decoder level pruned with the true occupancy)" if args.topk_from == "encoder" else "")),
             "clocks": clk,
             "e2e": {"value": total_points / (ms_e2e * 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
