@@ -14,8 +14,7 @@
 
 __global__ void __launch_bounds__(256) k_conv_bwd_weight(const float *__restrict__ feats, int cin, const int32_t *__restrict__ nbr,
                                                          long pitch, const uint32_t *__restrict__ tile_mask, long n_out,
-                                                         const float *__restrict__ gout, int cout, float *__restrict__ dw, int K,
-                                                         long tiles_per_slice) {
+                                                         const float *__restrict__ gout, int cout, float *__restrict__ dw, int K) {
     __shared__ float xs[BW_ROWS][BW_CI];
     __shared__ __align__(16) float gs[BW_ROWS][BW_CO];
     __shared__ int idx_s[BW_ROWS];
@@ -84,10 +83,9 @@ extern "C" int pcg_conv_bwd_weight_f32_sliced(const float *feats, int cin, const
     long slices = bwf_slices(K, cin, cout, tiles);
     const long n_w = (long)K * cin * cout;
     if (slices > 1 && (!scratch || scratch_bytes < (size_t)slices * n_w * sizeof(float))) slices = 1;
-    const long tps = cdiv(tiles, slices);
     float *dst = slices > 1 ? reinterpret_cast<float *>(scratch) : dweight;
     dim3 grid((unsigned)(K * slices), (unsigned)cdiv(cin, BW_CI), (unsigned)cdiv(cout, BW_CO));
-    k_conv_bwd_weight<<<grid, 256, 0, st>>>(feats, cin, nbr, nbr_pitch, tile_mask, n_out, gout, cout, dst, K, tps);
+    k_conv_bwd_weight<<<grid, 256, 0, st>>>(feats, cin, nbr, nbr_pitch, tile_mask, n_out, gout, cout, dst, K);
     PCG_LAUNCHED();
     if (slices > 1) {
         long blocks = cdiv(n_w, 256);
@@ -126,7 +124,7 @@ struct BwtParams {
     const int32_t *nbr;          // [K][pitch]
     const uint32_t *tile_mask;   // [tiles][4]
     float *partial;              // [S][K][cin][cout]
-    long n_out, pitch, tiles, tiles_per_slice;
+    long n_out, pitch, tiles;
     int cin, cout, K;
     int ci_chunks;               // 64-channel chunks of F actually present (cin_p / 64)
     int ci_chunks_p;             // rounded up to a multiple of 2 (blocks of M = 128; the padding chunk is zero-filled)
@@ -534,7 +532,6 @@ extern "C" int pcg_conv_bwd_weight_tc(const void *feats_bf16, int cin, const voi
     p.nbr = nbr; p.tile_mask = tile_mask; p.pitch = nbr_pitch; p.n_out = n_out;
     p.tiles = cdiv(n_out, BWT_ROWS);
     const long slices = bwt_slices(K, cin, cout, p.tiles);
-    p.tiles_per_slice = cdiv(p.tiles, slices);
     p.cin = cin; p.cout = cout; p.K = K;
     p.ci_chunks = (cin + 63) / 64; p.ci_chunks_p = (p.ci_chunks + 1) & ~1; p.co_chunks = (cout + 63) / 64;
     p.n_mma = (cout + 15) & ~15;
