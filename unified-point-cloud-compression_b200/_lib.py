@@ -126,7 +126,10 @@ def ptr(t):
 def raw_stream():
     """cudaStream_t of torch's current stream on the current device, as an int (the raw getter: ~0.3 us; building a
     torch.cuda.Stream object per C-ABI call cost several us of the ~15 us a launch takes on the host)."""
-    return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
+    try:
+        return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
+    except AttributeError:                       # private getters renamed in some torch build: the public (slower) path
+        return torch.cuda.current_stream().cuda_stream
 
 
 def stream():
