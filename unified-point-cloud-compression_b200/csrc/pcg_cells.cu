@@ -15,7 +15,7 @@
 
 #include <stdlib.h>
 
-#include "pcg_cells.cuh"
+#include "pcg_common.cuh"
 
 // valid-parent mask over the 27 e-indices (bit i = ex+1 + 3(ey+1) + 9(ez+1)) for child bit pattern b
 __device__ __forceinline__ uint32_t cells_valid_e(int b) {
@@ -154,22 +154,77 @@ extern "C" int pcg_cells_emit(const int32_t *cell_coords, const uint8_t *cell_ma
 // ---------------------------------------------------------------------------- 3x3x3 kernel map of the children
 // Same result as pcg_kernel_map(table of the children, children, ksize 3, ts_out) without a table of the children:
 // the 27 neighbours of a child live in the 2x2x2 cells around it; a neighbour's row is base[cell] + rank of its bit.
-__global__ void __launch_bounds__(128) k_cells_kernel_map3(const CellsMapArgs a, long n_out, int32_t *__restrict__ nbr, long pitch,
-                                                           uint32_t *__restrict__ tile_mask) {
+__global__ void __launch_bounds__(128) k_cells_kernel_map3(const uint64_t *__restrict__ cell_keys, const int32_t *__restrict__ cell_vals,
+                                                           uint64_t cmask, const int32_t *__restrict__ out_coords,
+                                                           const int32_t *__restrict__ out_cell, long n_out, int ts_out,
+                                                           const uint8_t *__restrict__ cell_mask, const int32_t *__restrict__ cell_base,
+                                                           int32_t *__restrict__ nbr, long pitch, uint32_t *__restrict__ tile_mask) {
+    __shared__ int s_base[8][128];
+    __shared__ uint8_t s_mask[8][128];
     __shared__ uint32_t smask_any;
     const int tid = threadIdx.x;
-    const long o = (long)blockIdx.x * 128 + tid;
+    long o = (long)blockIdx.x * 128 + tid;
+    bool live = o < n_out;
     if (tid == 0) smask_any = 0;
-    int rows[27];
-    cells_map3_row(a, o, o < n_out, rows);
-    uint32_t any_bits = 0;   // offsets (bit k) for which this warp has a neighbour
+    int4 c = live ? pcg_ld_coord(out_coords, o) : make_int4(0, 0, 0, 0);
+    const int ts_in = 2 * ts_out;
+    // cell origin and child bits
+    int Cx = pcg_floor_to(c.y, ts_in), Cy = pcg_floor_to(c.z, ts_in), Cz = pcg_floor_to(c.w, ts_in);
+    int bx = (c.y - Cx) / ts_out, by = (c.z - Cy) / ts_out, bz = (c.w - Cz) / ts_out;
+    int own = live ? __ldg(out_cell + o) : -1;
+    // the 7 neighbour-cell probes of a child are independent: their probe chains advance in lockstep, so the (dependent) loads of
+    // one chain overlap those of the others instead of running one chain after the other (the kernel is latency bound)
+    int cellv[8];
+    uint64_t key[8], slot[8];
+    uint32_t pend = 0;
+    cellv[0] = own;
 #pragma unroll
-    for (int k = 0; k < 27; ++k) {
-        nbr[(long)k * pitch + o] = rows[k];
-        if (__ballot_sync(0xffffffffu, rows[k] >= 0)) any_bits |= 1u << k;
+    for (int s = 1; s < 8; ++s) {
+        cellv[s] = -1;
+        const int x = Cx + ((s & 1) ? (bx ? ts_in : -ts_in) : 0);
+        const int y = Cy + ((s & 2) ? (by ? ts_in : -ts_in) : 0);
+        const int z = Cz + ((s & 4) ? (bz ? ts_in : -ts_in) : 0);
+        key[s] = pcg_pack(c.x, x, y, z);
+        slot[s] = pcg_mix(key[s]) & cmask;
+        if (live && pcg_in_range(c.x, x, y, z)) pend |= 1u << s;
     }
+    while (pend) {
+        uint64_t got[8];
+#pragma unroll
+        for (int s = 1; s < 8; ++s)
+            if ((pend >> s) & 1u) got[s] = __ldg(cell_keys + slot[s]);
+#pragma unroll
+        for (int s = 1; s < 8; ++s) {
+            if (!((pend >> s) & 1u)) continue;
+            if (got[s] == key[s]) { cellv[s] = __ldg(cell_vals + slot[s]); pend &= ~(1u << s); }
+            else if (got[s] == PCG_EMPTY_KEY) pend &= ~(1u << s);
+            else slot[s] = (slot[s] + 1) & cmask;
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const int cell = cellv[s];
+        s_base[s][tid] = cell >= 0 ? __ldg(cell_base + cell) : 0;
+        s_mask[s][tid] = cell >= 0 ? cell_mask[cell] : (uint8_t)0;
+    }
+    __syncthreads();
+    uint32_t any_bits = 0;   // offsets (bit k) for which this warp has a neighbour
+    int k = 0;
+#pragma unroll
+    for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx, ++k) {
+                int tx = bx + dx, ty = by + dy, tz = bz + dz;          // in [-1, 2]
+                int s = ((tx < 0 || tx > 1) ? 1 : 0) | ((ty < 0 || ty > 1) ? 2 : 0) | ((tz < 0 || tz > 1) ? 4 : 0);
+                int bit = (tx & 1) | ((ty & 1) << 1) | ((tz & 1) << 2);
+                uint32_t m = s_mask[s][tid];
+                int row = (live && ((m >> bit) & 1u)) ? s_base[s][tid] + __popc(m & ((1u << bit) - 1u)) : -1;
+                nbr[(long)k * pitch + o] = row;
+                if (__ballot_sync(0xffffffffu, row >= 0)) any_bits |= 1u << k;
+            }
     if (tile_mask) {
-        __syncthreads();
         if ((tid & 31) == 0) atomicOr(&smask_any, any_bits);
         __syncthreads();
         if (tid < 4) tile_mask[(long)blockIdx.x * 4 + tid] = tid == 0 ? smask_any : 0u;
@@ -183,8 +238,9 @@ extern "C" int pcg_cells_kernel_map3(const uint64_t *cell_keys, const int32_t *c
     PCG_CHECK_ARG(nbr_pitch == pcg_nbr_pitch(n_out), "pcg_cells_kernel_map3: nbr_pitch=%ld must be pcg_nbr_pitch(n_out)", nbr_pitch);
     PCG_CHECK_ARG(ts_out >= 1, "pcg_cells_kernel_map3: ts_out=%d", ts_out);
     if (n_out <= 0) return 0;
-    const CellsMapArgs a{cell_keys, cell_vals, (uint64_t)cell_cap - 1, out_coords, out_cell, cell_mask, cell_base, ts_out};
-    k_cells_kernel_map3<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(a, n_out, nbr, nbr_pitch, tile_mask);
+    k_cells_kernel_map3<<<(unsigned)cdiv(n_out, 128), 128, 0, as_stream(stream)>>>(
+        cell_keys, cell_vals, (uint64_t)cell_cap - 1, out_coords, out_cell, n_out, ts_out, cell_mask, cell_base, nbr, nbr_pitch,
+        tile_mask);
     PCG_LAUNCHED();
     return 0;
 }
