@@ -269,6 +269,14 @@ int pcg_prune_rows(const int32_t *coords, const float *feats, long n, int c, con
  * ME semantics) and move the feature rows once with pcg_gather_rows.  scratch >= pcg_scratch_bytes(n). */
 int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_n_out, void *scratch, size_t scratch_bytes,
                      void *stream);
+/* The same compaction WITHOUT caller scratch and without any allocation (no cudaMalloc / cudaFree / allocating library call): the
+ * scratch is a file-scope device array inside libpcg.so, sized for n <= PCG_MASK_TO_ROWS_STATIC_MAX items (4.0 MiB, held by every
+ * GPU that loads the library until exit); larger n is rejected with an error.  For callers that cannot allocate: code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc.  Output identical to pcg_mask_to_rows.  All calls share
+ * the array (its zero-initialised words are cleared on `stream` at every call): calls that OVERLAP on the GPU race -- keep them on
+ * one stream or order them.  No counterpart in the reference. */
+#define PCG_MASK_TO_ROWS_STATIC_MAX (4L * 1024 * 1024)
+int pcg_mask_to_rows_static(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_n_out, void *stream);
 /* out_coords[r] = coords[rows[r]], out_feats[r] = feats[rows[r]] (c fp32 channels) for r < n_rows; either pair may be NULL. */
 int pcg_gather_rows(const int32_t *coords, const float *feats, int c, const int32_t *rows, long n_rows, int32_t *out_coords,
                     float *out_feats, void *stream);

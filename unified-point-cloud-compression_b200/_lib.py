@@ -69,6 +69,7 @@ _PROTOS = {
     "pcg_prune_rows": (_I, [_P, _P, _L, _I, _P, _P, _P, _P, _P, _SZ, _P]),
     "pcg_nn_search": (_I, [_P, _P, _L, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P]),
     "pcg_mask_to_rows": (_I, [_P, _L, _P, _P, _P, _SZ, _P]),
+    "pcg_mask_to_rows_static": (_I, [_P, _L, _P, _P, _P]),
     "pcg_gather_rows": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
     "pcg_gather_rows_bf16": (_I, [_P, _P, _I, _P, _L, _P, _P, _P]),
     "pcg_color_jitter_scratch_bytes": (_SZ, []),

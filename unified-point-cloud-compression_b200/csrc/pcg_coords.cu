@@ -464,6 +464,50 @@ extern "C" int pcg_mask_to_rows(const uint8_t *mask, long n, int32_t *out_rows, 
     return pcg_compact(n, FlagMask{mask}, EmitIndex{out_rows}, d_n_out, s, as_stream(stream));
 }
 
+// ---------------------------------------------------------------------------- pcg_mask_to_rows without caller scratch
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the same
+// compaction as pcg_mask_to_rows with its scratch in a file-scope device array of a stated maximum size.  Every GPU that loads
+// the library holds the array (4.0 MiB) until exit.  The array's NAME is a host-side stand-in in host code, not a device address:
+// the address is taken once per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// All calls share the array: the compaction clears the words that must start at zero (tile states, ticket) on the caller's
+// stream at every call, and calls that overlap on the GPU (different streams, no ordering between them) RACE -- serialise them.
+#define PCG_STATIC_MAX_ITEMS (4L * 1024 * 1024)
+// = pcg_compact_scratch_bytes(PCG_STATIC_MAX_ITEMS) rounded up to 256: item flags / tile states + per-tile counts + slack
+#define PCG_STATIC_SCRATCH_BYTES (PCG_STATIC_MAX_ITEMS + (PCG_STATIC_MAX_ITEMS / PCG_CHUNK + 2) * 4 + 256 + 248)
+static __device__ __align__(256) unsigned char g_static_scratch[PCG_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+static int static_scratch_address(void **out) {
+    static std::mutex mu;
+    static void *addr[64] = {nullptr};            // per device ordinal
+    int dev = -1;
+    PCG_CUDA(cudaGetDevice(&dev));
+    PCG_CHECK_ARG(dev >= 0 && dev < 64, "pcg_mask_to_rows_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);       // device `dev` is current: its copy of the array
+        if (e != cudaSuccess || p == nullptr)
+            return pcg_fail("pcg_mask_to_rows_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return 0;
+}
+
+extern "C" int pcg_mask_to_rows_static(const uint8_t *mask, long n, int32_t *out_rows, int32_t *d_n_out, void *stream) {
+    PCG_CHECK_ARG(n >= 0, "pcg_mask_to_rows_static: n=%ld", n);
+    PCG_CHECK_ARG(n <= PCG_STATIC_MAX_ITEMS, "pcg_mask_to_rows_static: n=%ld exceeds the built-in scratch (at most %ld items; use "
+                  "pcg_mask_to_rows with caller scratch beyond that)", n, (long)PCG_STATIC_MAX_ITEMS);
+    static_assert(PCG_STATIC_SCRATCH_BYTES % 256 == 0, "scratch array size must keep the 256-byte granularity");
+    PCG_CHECK_ARG(pcg_compact_scratch_bytes(PCG_STATIC_MAX_ITEMS) <= (size_t)PCG_STATIC_SCRATCH_BYTES, "pcg_mask_to_rows_static: scratch array too small");
+    void *scratch = nullptr;
+    if (int rc = static_scratch_address(&scratch)) return rc;
+    PcgScratch s;
+    PCG_CHECK_ARG(pcg_carve_scratch(scratch, PCG_STATIC_SCRATCH_BYTES, n, s), "pcg_mask_to_rows_static: scratch carve failed");
+    return pcg_compact(n, FlagMask{mask}, EmitIndex{out_rows}, d_n_out, s, as_stream(stream));
+}
+
 // out[r] = src[rows[r]] for r < n_rows: coordinate rows (int32 x 4, src_coords/out_coords optional) and fp32 feature rows of c
 // channels (optional), one warp per row.
 // bf16 source rows (c % 8 == 0 channels, 16-byte aligned rows) -> fp32 output rows: the survivors of a prune whose candidates
