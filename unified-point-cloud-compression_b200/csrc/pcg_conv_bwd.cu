@@ -503,10 +503,27 @@ static bool bwt_k_inner(int K, int cin, int cout, long tiles) {      // narrow o
 
 static long bwt_slices(int K, int cin, int cout, long tiles) {
     if (bwt_k_inner(K, cin, cout, tiles)) return PCG_SMS;      // one CTA per SM, each a strided slice of the tiles
-    long s = (2L * PCG_SMS) / K;             // at most two full waves of CTAs (one CTA per SM: the operand ring takes most of the shared memory)
-    if (s > tiles) s = tiles;
-    if (s > 64) s = 64;
-    return s < 1 ? 1 : s;
+    // One CTA per SM (the operand ring takes most of the shared memory) and no dynamic scheduling: K * slices CTAs run in waves of
+    // 148.  Base rule: about two waves.  Large outputs (>= 1024 tiles per slice: a CTA must keep enough ACTIVE tiles to amortise
+    // its pipeline fill and its 64 KB partial block) may take more slices, and then the count that fills the last wave best is
+    // chosen (K = 125 with 2 slices was 250 CTAs = 1.69 waves: ncu showed the second wave 31 % empty; 13 slices = 10.98 waves:
+    // 12.4 -> 10.0 ms on the 125x128x32 layer of the training batch); partial blocks stay below 256 MiB.
+    long lo = (2L * PCG_SMS) / K;
+    if (lo > tiles) lo = tiles;
+    if (lo > 64) lo = 64;
+    if (lo < 1) lo = 1;
+    long hi = tiles / 1024 < 64 ? tiles / 1024 : 64;
+    const long by_mem = (256L << 20) / ((long)K * cin * cout * 4);
+    if (hi > by_mem) hi = by_mem;
+    if (hi <= lo) return lo;
+    long best = lo;
+    double best_eff = 0.0;
+    for (long c = lo; c <= hi; ++c) {
+        const long ctas = (long)K * c;
+        const double eff = (double)ctas / (double)(cdiv(ctas, PCG_SMS) * PCG_SMS);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = c; }
+    }
+    return best;
 }
 
 extern "C" size_t pcg_conv_bwd_weight_tc_scratch_bytes(int K, int cin, int cout, long n_out) {
