@@ -185,6 +185,9 @@ def tiny_codec_roundtrip(pkg, device, width=32, seed=0, mode="auto", return_clou
     rrec = ref.decode_block(renc["y_points"], renc["z_symbols"], renc["y_symbols"], renc["k"], [0.5, 0.5])
     ia, ib = align_rows(rec[:, :3], rrec[:, :3])
     assert len(rec) == len(rrec)
+    # random-init weights in bf16 mode: a sanity bound only (top-k flips near barely separated logits compound over three levels).
+    # The parity gate of the timed bf16 mode is test_trained_codec_matches_fp32_oracle (trained weights: min_overlap 0.99, symbols
+    # 99.5 %, PSNR within 0.05 dB), which passes min_overlap / max_symbol_mismatch explicitly.
     need = min_overlap if min_overlap is not None else (0.99 if mode == "f32" else 0.25)
     assert len(ia) >= need * len(rrec), f"decoded geometry overlap {len(ia)}/{len(rrec)}"
     assert np.abs(rec[ia, 3:] - rrec[ib, 3:]).mean() < 0.02
