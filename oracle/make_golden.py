@@ -73,6 +73,31 @@ def make(name, cfg_name, seed, q):
     print(name, "points", len(pts), "k", ks, "bytes y/z", len(bits[0][0][0]), len(bits[0][1][0]), "rec", tuple(rec.shape))
 
 
+def make_multiblock(name="ref_multiblock", seed=4, q=(0.5, 0.5), block_size=24):
+    """The reference's own block loop (model/model.py:121-176 compress, :225-238 decompress) on a cloud that falls into several
+    blocks: partition order, per-block latent coordinates / level sizes / strings, and the concatenated reconstruction."""
+    cfg = small_config("CVPR_inverse_scaling")
+    net = shim.reference_model(cfg, seed=seed)
+    spread_weights(net)
+    pts, rgb = synth.small_cloud(seed=seed + 1, radius=20.0, centre=(32, 32, 32), n_samples=40000)
+    pc = torch.from_numpy(np.concatenate([pts.astype(np.float32), rgb], axis=1))
+    qt = torch.tensor([q], dtype=torch.float32)
+    with torch.no_grad():
+        bits, shapes, ks, coords, qv = net.compress(pc.clone(), qt, block_size=block_size)
+        rec = net.decompress(coordinates=coords, strings=bits, shape=shapes, k=ks, q_vals=qv)
+    per_block = {}
+    for i in range(len(bits)):
+        per_block[f"y_coords_{i}"] = coords[i].numpy()
+        per_block[f"k_{i}"] = np.asarray(ks[i]).reshape(-1)
+        per_block[f"z_shape_{i}"] = np.asarray(shapes[i])
+        per_block[f"y_string_{i}"] = np.frombuffer(bits[i][0][0], np.uint8)
+        per_block[f"z_string_{i}"] = np.frombuffer(bits[i][1][0], np.uint8)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), cfg_name="CVPR_inverse_scaling", width=8, q=np.asarray(q, np.float32),
+                        block_size=block_size, n_blocks=len(bits), points=pts, colors=rgb, reconstruction=rec.numpy(), **per_block,
+                        **{"sd/" + k: v.numpy() for k, v in net.state_dict().items()})
+    print(name, "points", len(pts), "blocks", len(bits), "k", [np.asarray(k).reshape(-1).tolist() for k in ks][:4], "rec", tuple(rec.shape))
+
+
 def make_losses(name="ref_losses", seed=3, q=(0.4, 0.8), lam=(0.7, 1.3)):
     """Loss values of the reference's UNMODIFIED loss.py (/root/reference/loss.py:9-274: Loss, BPPLoss, ColorLoss,
     Multiscale_FocalLoss, ShepardsLoss with utils.overlapping_mask) on the training forward of its own model, both for the
@@ -119,10 +144,12 @@ def make_losses(name="ref_losses", seed=3, q=(0.4, 0.8), lam=(0.7, 1.3)):
 if __name__ == "__main__":
     assert shim.available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
-    what = sys.argv[1:] or ["codec", "losses"]
+    what = sys.argv[1:] or ["codec", "losses", "multiblock"]
     if "codec" in what:
         make("ref_inverse_scaling", "CVPR_inverse_scaling", 0, (0.5, 0.5))
         make("ref_inverse_nn", "CVPR_inverse_nn", 1, (0.2, 0.9))
         make("ref_fixed_R1", "CVPR_inverse_scaling_fixed_R1", 2, (0.0, 0.0))
     if "losses" in what:
         make_losses()
+    if "multiblock" in what:
+        make_multiblock()

@@ -370,3 +370,48 @@ def test_batched_blocks_equal_serial_blocks(pkg, dev, mode):
     canon = lambda a: a[np.lexsort(a.T[::-1])]          # full-row order: a voxel predicted by two blocks appears twice, colours may differ
     assert serial.shape == batched.shape and serial.shape[0] == len(pts)
     assert np.array_equal(canon(serial), canon(batched))
+
+
+def test_multiblock_compress_decompress_against_reference_golden(pkg, dev):
+    """The block loop (model/model.py:121-176, :225-238; evaluate.py:45 codes 11-bit frames in blocks of 512) against the
+    reference's own run of it over the CPU oracle (tests/golden/ref_multiblock.npz: 8 blocks): same partition order, per-block
+    level sizes, latent coordinates and hyper-latent shapes; strings equal unless a symbol sits on a rounding boundary; and the
+    product's decode of the REFERENCE's strings reproduces the reference reconstruction (fp32 mode)."""
+    from oracle import rans_ref
+    z, sd = load_golden("ref_multiblock")
+    net = build_product_model(pkg, golden_config(z), sd, dev)
+    q = torch.from_numpy(z["q"]).reshape(1, 2).to(dev)
+    pc = torch.from_numpy(np.concatenate([z["points"].astype(np.float32), z["colors"]], axis=1)).to(dev)
+    nb = int(z["n_blocks"])
+    prev = pkg.sparse_ops.set_conv_mode("f32")
+    try:
+        with torch.no_grad():
+            bits, shapes, ks, coords, qv = net.compress(pc, q, block_size=int(z["block_size"]))
+        assert len(bits) == nb
+        em = net.entropy_model
+        eb_t = [t.cpu().numpy() for t in (em.entropy_bottleneck._quantized_cdf, em.entropy_bottleneck._cdf_length, em.entropy_bottleneck._offset)]
+        C = em.entropy_bottleneck.channels
+        same_strings = 0
+        for i in range(nb):
+            assert [int(v[0]) for v in ks[i]] == z[f"k_{i}"].tolist(), i
+            assert shapes[i] == z[f"z_shape_{i}"].tolist(), i
+            ia, _ = align_rows(coords[i].cpu().numpy(), z[f"y_coords_{i}"])
+            assert len(ia) == coords[i].shape[0] == len(z[f"y_coords_{i}"]), i
+            z_idx = np.repeat(np.arange(C), int(z[f"z_shape_{i}"][0]))
+            mine_z = rans_ref.decode_with_indexes(bits[i][1][0], z_idx, *eb_t)
+            ref_z = rans_ref.decode_with_indexes(z[f"z_string_{i}"].tobytes(), z_idx, *eb_t)
+            assert np.abs(mine_z - ref_z).max() <= 1 and (mine_z != ref_z).mean() <= 0.02, i
+            same_strings += int(bits[i][1][0] == z[f"z_string_{i}"].tobytes() and bits[i][0][0] == z[f"y_string_{i}"].tobytes())
+        assert same_strings >= nb // 2, f"only {same_strings} of {nb} blocks have byte-identical strings"
+        ref_strings = [[[z[f"y_string_{i}"].tobytes()], [z[f"z_string_{i}"].tobytes()]] for i in range(nb)]
+        ref_coords = [torch.from_numpy(z[f"y_coords_{i}"]).to(dev) for i in range(nb)]
+        with torch.no_grad():
+            rec = net.decompress(coordinates=ref_coords, strings=ref_strings, shape=[z[f"z_shape_{i}"].tolist() for i in range(nb)],
+                                 k=[[[int(v)] for v in z[f"k_{i}"]] for i in range(nb)], q_vals=[q] * nb).cpu().numpy()
+    finally:
+        pkg.sparse_ops.set_conv_mode(prev)
+    ref = z["reconstruction"]
+    assert len(rec) == len(ref)
+    ia, ib = align_rows(rec[:, :3], ref[:, :3])
+    assert len(ia) >= 0.99 * len(np.unique(ref[:, :3], axis=0)), f"decoded geometry overlap {len(ia)}/{len(ref)}"
+    assert np.abs(rec[ia, 3:] - ref[ib, 3:]).max() <= 1.0 / 255 + 1e-6
