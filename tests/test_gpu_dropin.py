@@ -73,6 +73,16 @@ def test_reference_code_on_drop_in_matches_golden(pkg, dev, name, mode):
 
 @needs_reference
 @pytest.mark.gpu
+def test_reference_block_loop_on_drop_in_matches_golden(pkg, dev):
+    """The reference's own block loop (model/model.py:121-176, :225-238) over the product packages on a cloud of 8 blocks, against
+    the fixture the same code produced over the CPU oracle (tests/golden/ref_multiblock.npz)."""
+    from tests.test_gpu_model import _multiblock_roundtrip
+    with reference_on_product(pkg) as ref:
+        _multiblock_roundtrip(pkg, dev, make_net=lambda c, s, d: _reference_net(ref, c, s, d))
+
+
+@needs_reference
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["f32", "auto"])
 def test_reference_code_on_drop_in_equals_mirror(pkg, dev, mode):
     """Same weights, same cloud: the reference's host code on the drop-in packages and the product's mirror produce the SAME

@@ -377,9 +377,15 @@ def test_multiblock_compress_decompress_against_reference_golden(pkg, dev):
     reference's own run of it over the CPU oracle (tests/golden/ref_multiblock.npz: 8 blocks): same partition order, per-block
     level sizes, latent coordinates and hyper-latent shapes; strings equal unless a symbol sits on a rounding boundary; and the
     product's decode of the REFERENCE's strings reproduces the reference reconstruction (fp32 mode)."""
+    _multiblock_roundtrip(pkg, dev)
+
+
+def _multiblock_roundtrip(pkg, dev, make_net=None):
+    """make_net(config, state_dict, device): model factory (default: the product's mirror; tests/test_gpu_dropin.py passes the
+    reference's own UnifiedModel over the drop-in packages)."""
     from oracle import rans_ref
     z, sd = load_golden("ref_multiblock")
-    net = build_product_model(pkg, golden_config(z), sd, dev)
+    net = (make_net or (lambda c, s_, d: build_product_model(pkg, c, s_, d)))(golden_config(z), sd, dev)
     q = torch.from_numpy(z["q"]).reshape(1, 2).to(dev)
     pc = torch.from_numpy(np.concatenate([z["points"].astype(np.float32), z["colors"]], axis=1)).to(dev)
     nb = int(z["n_blocks"])
